@@ -1,0 +1,374 @@
+// TEST INFRASTRUCTURE ONLY — C-ABI driver around the UNMODIFIED reference.
+//
+// This translation unit textually includes the reference's src/mgr.cpp from
+// where it lies under $(REF) (never copied into this repo) so that the harness
+// can reach Manager::CPUImpl and, through it, each world's ECS context.  All
+// simulation arithmetic executed through these entry points is the reference's
+// own CPU backend; the harness only constructs, steps and reads.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+// --impl reference legs may load the resulting library.
+
+#include <algorithm>
+#include <array>
+#include <atomic>
+#include <charconv>
+#include <chrono>
+#include <filesystem>
+#include <fstream>
+#include <iostream>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+#include <sched.h>
+#include <pthread.h>
+
+// Headers that forward-declare nested types with an explicit access level
+// must be seen before the access override below.
+#include <madrona/memory.hpp>
+
+// Read-only access to engine internals (BVH nodes, RNG counters).
+#define private public
+#define protected public
+#include <mgr.cpp>
+#undef private
+#undef protected
+
+#include "ref_dump.h"
+
+using namespace GPUHideSeek;
+namespace bp = madrona::phys::broadphase;
+
+namespace {
+
+struct Handle {
+    Manager *mgr;
+    Manager::CPUImpl *impl;
+    int numWorlds;
+    int agentsPerWorld;
+};
+
+inline Manager::CPUImpl *cpuImpl(Manager *m)
+{
+    return static_cast<Manager::CPUImpl *>(m->impl_);
+}
+
+}
+
+extern "C" {
+
+// num_threads <= 0: use every core in the affinity mask (reference default).
+void *hsref_create(int num_worlds, uint32_t sim_flags, uint32_t seed,
+                   int min_hiders, int max_hiders,
+                   int min_seekers, int max_seekers, int num_threads)
+{
+    cpu_set_t orig;
+    pthread_getaffinity_np(pthread_self(), sizeof(orig), &orig);
+
+    if (num_threads > 0) {
+        cpu_set_t limited;
+        CPU_ZERO(&limited);
+        int taken = 0;
+        for (int i = 0; i < CPU_SETSIZE && taken < num_threads; i++) {
+            if (CPU_ISSET(i, &orig)) {
+                CPU_SET(i, &limited);
+                taken++;
+            }
+        }
+        pthread_setaffinity_np(pthread_self(), sizeof(limited), &limited);
+    }
+
+    Manager *mgr = new Manager(Manager::Config {
+        .execMode = madrona::ExecMode::CPU,
+        .gpuID = 0,
+        .numWorlds = (uint32_t)num_worlds,
+        .simFlags = (SimFlags)sim_flags,
+        .randSeed = seed,
+        .minHiders = (uint32_t)min_hiders,
+        .maxHiders = (uint32_t)max_hiders,
+        .minSeekers = (uint32_t)min_seekers,
+        .maxSeekers = (uint32_t)max_seekers,
+        .numPBTPolicies = 0,
+        .enableBatchRenderer = false,
+    });
+
+    pthread_setaffinity_np(pthread_self(), sizeof(orig), &orig);
+
+    Handle *h = new Handle {
+        mgr, cpuImpl(mgr), num_worlds, max_hiders + max_seekers,
+    };
+    return h;
+}
+
+void hsref_destroy(void *hp)
+{
+    Handle *h = (Handle *)hp;
+    delete h->mgr;
+    delete h;
+}
+
+void hsref_init(void *hp) { ((Handle *)hp)->mgr->init(); }
+void hsref_step(void *hp) { ((Handle *)hp)->mgr->step(); }
+
+// Worker count the reference pool was created with (= CPUs in the affinity
+// mask at construction, M/src/mw/cpu_exec.cpp:30-56,102).
+int hsref_affinity_cpus()
+{
+    cpu_set_t cur;
+    pthread_getaffinity_np(pthread_self(), sizeof(cur), &cur);
+    return CPU_COUNT(&cur);
+}
+
+void *hsref_tensor(void *hp, int export_id)
+{
+    Handle *h = (Handle *)hp;
+    return h->impl->cpuExec.getExported((uint32_t)export_id);
+}
+
+int hsref_checkpoint_bytes() { return (int)sizeof(Checkpoint); }
+
+void hsref_trigger_reset(void *hp, int world, int level)
+{
+    ((Handle *)hp)->mgr->triggerReset(world, level);
+}
+
+void hsref_set_action(void *hp, int agent_row, int x, int y, int r, int g, int l)
+{
+    ((Handle *)hp)->mgr->setAction(agent_row, x, y, r, g != 0, l != 0);
+}
+
+void hsref_save_checkpoint(void *hp, int world) { ((Handle *)hp)->mgr->saveCheckpoint(world); }
+void hsref_load_checkpoint(void *hp, int world) { ((Handle *)hp)->mgr->loadCheckpoint(world); }
+
+static void fillBody(Engine &ctx, Entity e, int archetype, hsref_body *b)
+{
+    using namespace madrona;
+    using namespace madrona::phys;
+    using namespace madrona::base;
+
+    Loc loc = ctx.loc(e);
+    b->entity_id = e.id;
+    b->archetype = archetype;
+    b->row = loc.row;
+    b->obj_id = ctx.get<ObjectID>(e).idx;
+    b->response = (int32_t)ctx.get<ResponseType>(e);
+    b->owner = (int32_t)ctx.get<OwnerTeam>(e);
+    b->leaf_id = ctx.get<bp::LeafID>(e).id;
+    b->grab_joint = -1;
+    if (archetype == 1) {
+        Entity j = ctx.get<GrabData>(e).constraintEntity;
+        b->grab_joint = (j == Entity::none()) ? -1 : j.id;
+    }
+    Vector3 p = ctx.get<Position>(e);
+    Quat q = ctx.get<Rotation>(e);
+    Diag3x3 s = ctx.get<Scale>(e);
+    Velocity v = ctx.get<Velocity>(e);
+    Vector3 f = ctx.get<ExternalForce>(e);
+    Vector3 t = ctx.get<ExternalTorque>(e);
+    b->pos[0] = p.x; b->pos[1] = p.y; b->pos[2] = p.z;
+    b->rot[0] = q.w; b->rot[1] = q.x; b->rot[2] = q.y; b->rot[3] = q.z;
+    b->scale[0] = s.d0; b->scale[1] = s.d1; b->scale[2] = s.d2;
+    b->vel[0] = v.linear.x; b->vel[1] = v.linear.y; b->vel[2] = v.linear.z;
+    b->vel[3] = v.angular.x; b->vel[4] = v.angular.y; b->vel[5] = v.angular.z;
+    b->ext_force[0] = f.x; b->ext_force[1] = f.y; b->ext_force[2] = f.z;
+    b->ext_torque[0] = t.x; b->ext_torque[1] = t.y; b->ext_torque[2] = t.z;
+}
+
+int hsref_dump_world(void *hp, int world, hsref_world *out)
+{
+    using namespace madrona;
+    using namespace madrona::phys;
+
+    Handle *h = (Handle *)hp;
+    Engine &ctx = h->impl->cpuExec.getWorldContext(world);
+    Sim &sim = h->impl->cpuExec.getWorldData(world);
+
+    memset(out, 0, sizeof(*out));
+
+    out->cur_episode_step = (int32_t)sim.curEpisodeStep;
+    out->cur_world_episode = (int32_t)sim.curWorldEpisode;
+    out->episode_key[0] = sim.curEpisodeRNDCounter.a;
+    out->episode_key[1] = sim.curEpisodeRNDCounter.b;
+    out->rng_key[0] = sim.rng.k_.a;
+    out->rng_key[1] = sim.rng.k_.b;
+    out->rng_count = sim.rng.count_;
+    out->num_hiders = sim.numHiders;
+    out->num_seekers = sim.numSeekers;
+    out->num_active_agents = (int32_t)sim.numActiveAgents;
+    out->num_obstacles = sim.numObstacles;
+    out->num_boxes = (int32_t)sim.numActiveBoxes;
+    out->num_ramps = (int32_t)sim.numActiveRamps;
+    out->hider_team_reward = sim.hiderTeamReward.load_relaxed();
+    out->seekers_first = ctx.singleton<TeamState>().seekersFirst ? 1 : 0;
+    out->running_scores[0] = ctx.singleton<EpisodeStats>().runningScores[0];
+    out->running_scores[1] = ctx.singleton<EpisodeStats>().runningScores[1];
+
+    for (int i = 0; i < sim.numObstacles && i < HSREF_MAX_BODIES; i++) {
+        out->obstacles[i] = sim.obstacles[i].id;
+    }
+    for (int i = 0; i < 9; i++) {
+        out->boxes[i] = i < sim.numActiveBoxes ? sim.boxes[i].id : -1;
+        out->box_sizes[i][0] = sim.boxSizes[i].x;
+        out->box_sizes[i][1] = sim.boxSizes[i].y;
+        out->box_sizes[i][2] = sim.boxSizes[i].z;
+    }
+    for (int i = 0; i < 2; i++) {
+        out->ramps[i] = i < sim.numActiveRamps ? sim.ramps[i].id : -1;
+    }
+    for (int i = 0; i < 3; i++) {
+        out->hiders[i] = i < sim.numHiders ? sim.hiders[i].id : -1;
+        out->seekers[i] = i < sim.numSeekers ? sim.seekers[i].id : -1;
+    }
+    for (int i = 0; i < HSREF_MAX_AGENTS; i++) {
+        out->agent_iface_sim[i] = -1;
+        if (i < sim.maxAgentsPerWorld) {
+            Entity se = ctx.get<SimEntity>(sim.agentInterfaces[i]).e;
+            out->agent_iface_sim[i] = (se == Entity::none()) ? -1 : se.id;
+        }
+    }
+
+    // Bodies in ECS iteration order (src/core/state.cpp query order:
+    // ascending archetype id => DynamicObject then DynAgent; rows in table
+    // order, holes skipped).
+    int nb = 0;
+    {
+        auto q = ctx.query<Entity, OwnerTeam, bp::LeafID>();
+        ctx.iterateQuery(q, [&](Entity e, OwnerTeam &, bp::LeafID &) {
+            if (nb >= HSREF_MAX_BODIES) return;
+            int arch = ctx.getSafe<GrabData>(e).valid() ? 1 : 0;
+            fillBody(ctx, e, arch, &out->bodies[nb++]);
+        });
+    }
+    out->num_bodies = nb;
+
+    int nj = 0;
+    {
+        auto q = ctx.query<Entity, JointConstraint>();
+        ctx.iterateQuery(q, [&](Entity e, JointConstraint &j) {
+            if (nj >= HSREF_MAX_JOINTS) return;
+            hsref_joint &o = out->joints[nj++];
+            o.entity_id = e.id;
+            o.e1 = j.e1.id;
+            o.e2 = j.e2.id;
+            Quat a1 = j.fixed.attachRot1, a2 = j.fixed.attachRot2;
+            o.attach1[0] = a1.w; o.attach1[1] = a1.x; o.attach1[2] = a1.y; o.attach1[3] = a1.z;
+            o.attach2[0] = a2.w; o.attach2[1] = a2.x; o.attach2[2] = a2.y; o.attach2[3] = a2.z;
+            o.separation = j.fixed.separation;
+            o.r1[0] = j.r1.x; o.r1[1] = j.r1.y; o.r1[2] = j.r1.z;
+            o.r2[0] = j.r2.x; o.r2[1] = j.r2.y; o.r2[2] = j.r2.z;
+        });
+    }
+    out->num_joints = nj;
+
+    bp::BVH &bvh = ctx.singleton<bp::BVH>();
+    int nl = bvh.num_leaves_.load_relaxed();
+    out->bvh_num_leaves = nl;
+    out->bvh_num_nodes = (int32_t)bvh.num_nodes_;
+    out->bvh_force_rebuild = bvh.force_rebuild_ ? 1 : 0;
+    static_assert(sizeof(bp::BVH::Node) == sizeof(hsref_node));
+    int nn = std::min<int>((int)bvh.num_nodes_, HSREF_MAX_NODES);
+    memcpy(out->nodes, bvh.nodes_, sizeof(hsref_node) * nn);
+    for (int i = 0; i < nl && i < HSREF_MAX_BODIES; i++) {
+        math::AABB a = bvh.leaf_aabbs_[i];
+        out->leaf_aabbs[i][0] = a.pMin.x; out->leaf_aabbs[i][1] = a.pMin.y;
+        out->leaf_aabbs[i][2] = a.pMin.z; out->leaf_aabbs[i][3] = a.pMax.x;
+        out->leaf_aabbs[i][4] = a.pMax.y; out->leaf_aabbs[i][5] = a.pMax.z;
+        out->leaf_parents[i] = bvh.leaf_parents_[i];
+        out->leaf_entities[i] = bvh.leaf_entities_[i].id;
+        out->leaf_obj_ids[i] = bvh.leaf_obj_ids_[i].idx;
+    }
+
+    return 0;
+}
+
+int hsref_world_dump_bytes() { return (int)sizeof(hsref_world); }
+int hsref_object_dump_bytes() { return (int)sizeof(hsref_object); }
+
+// Processed asset tables (ObjectManager) — what every world reads at run time.
+int hsref_dump_objects(void *hp, hsref_object *out /* [HSREF_NUM_OBJECTS] */)
+{
+    using namespace madrona;
+    using namespace madrona::phys;
+
+    Handle *h = (Handle *)hp;
+    ObjectManager &om = h->impl->physicsLoader.getObjectManager();
+
+    for (int o = 0; o < HSREF_NUM_OBJECTS; o++) {
+        hsref_object &d = out[o];
+        memset(&d, 0, sizeof(d));
+        uint32_t prim_idx = om.rigidBodyPrimitiveOffsets[o];
+        if (om.rigidBodyPrimitiveCounts[o] != 1) return -1;
+        const CollisionPrimitive &p = om.collisionPrimitives[prim_idx];
+        d.prim_type = (int32_t)p.type;
+        math::AABB pa = om.primitiveAABBs[prim_idx];
+        math::AABB oa = om.rigidBodyAABBs[o];
+        float pav[6] = {pa.pMin.x, pa.pMin.y, pa.pMin.z, pa.pMax.x, pa.pMax.y, pa.pMax.z};
+        float oav[6] = {oa.pMin.x, oa.pMin.y, oa.pMin.z, oa.pMax.x, oa.pMax.y, oa.pMax.z};
+        memcpy(d.prim_aabb, pav, sizeof(pav));
+        memcpy(d.obj_aabb, oav, sizeof(oav));
+        const RigidBodyMetadata &md = om.metadata[o];
+        d.inv_mass = md.mass.invMass;
+        d.inv_inertia[0] = md.mass.invInertiaTensor.x;
+        d.inv_inertia[1] = md.mass.invInertiaTensor.y;
+        d.inv_inertia[2] = md.mass.invInertiaTensor.z;
+        d.mu_s = md.friction.muS;
+        d.mu_d = md.friction.muD;
+        if (p.type == CollisionPrimitive::Type::Hull) {
+            const geo::HalfEdgeMesh &m = p.hull.halfEdgeMesh;
+            if (m.numVertices > HSREF_MAX_HULL_VERTS ||
+                m.numFaces > HSREF_MAX_HULL_FACES ||
+                m.numHalfEdges > HSREF_MAX_HULL_HEDGES) return -2;
+            d.num_verts = m.numVertices;
+            d.num_faces = m.numFaces;
+            d.num_hedges = m.numHalfEdges;
+            for (uint32_t i = 0; i < m.numVertices; i++) {
+                d.verts[i][0] = m.vertices[i].x;
+                d.verts[i][1] = m.vertices[i].y;
+                d.verts[i][2] = m.vertices[i].z;
+            }
+            for (uint32_t i = 0; i < m.numFaces; i++) {
+                d.planes[i][0] = m.facePlanes[i].normal.x;
+                d.planes[i][1] = m.facePlanes[i].normal.y;
+                d.planes[i][2] = m.facePlanes[i].normal.z;
+                d.planes[i][3] = m.facePlanes[i].d;
+                d.face_base_hedge[i] = m.faceBaseHalfEdges[i];
+            }
+            for (uint32_t i = 0; i < m.numHalfEdges; i++) {
+                d.hedges[i][0] = m.halfEdges[i].next;
+                d.hedges[i][1] = m.halfEdges[i].rootVertex;
+                d.hedges[i][2] = m.halfEdges[i].face;
+            }
+        }
+    }
+    return 0;
+}
+
+// Wall-clock timing of K reference steps with uniform random move actions,
+// mirroring scripts/benchmark.py:74-88 (x,y <- randint(-5,5) every step).
+double hsref_bench(void *hp, int warmup, int steps, uint32_t action_seed)
+{
+    Handle *h = (Handle *)hp;
+    int32_t *actions = (int32_t *)hsref_tensor(hp, (int)ExportID::Action);
+    int rows = h->numWorlds * h->agentsPerWorld;
+    uint64_t s = 0x9E3779B97F4A7C15ull ^ action_seed;
+    auto next = [&]() {
+        s ^= s << 13; s ^= s >> 7; s ^= s << 17;
+        return (uint32_t)(s >> 32);
+    };
+    auto fill = [&]() {
+        for (int i = 0; i < rows; i++) {
+            actions[i * 5 + 0] = (int32_t)(next() % 10) - 5;
+            actions[i * 5 + 1] = (int32_t)(next() % 10) - 5;
+        }
+    };
+    for (int i = 0; i < warmup; i++) { fill(); h->mgr->step(); }
+    auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < steps; i++) { fill(); h->mgr->step(); }
+    auto t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+}
