@@ -55,3 +55,17 @@ Span<SourceTexture> ImageImporter::importImages(StackAlloc &, Span<const char * 
 void ImageImporter::deallocImportedImages(Span<SourceTexture>) { HS_STUB_ABORT(); }
 
 }
+
+// ---------------------------------------------------------------------------
+// Deterministic sinf/cosf/sincosf.  The shared library is
+// linked with -Bsymbolic-functions so every sinf/cosf/sincosf call inside the
+// reference objects binds to these definitions instead of libm's; no reference
+// source is edited.  The deviation from glibc is <= 1 ulp and is the ONLY
+// arithmetic in the oracle that is not the reference's own.
+#include "../include/hideseek/detmath.h"
+
+extern "C" {
+float sinf(float x) noexcept { return hs_det_sinf(x); }
+float cosf(float x) noexcept { return hs_det_cosf(x); }
+void sincosf(float x, float *s, float *c) noexcept { hs_det_sincosf(x, s, c); }
+}
