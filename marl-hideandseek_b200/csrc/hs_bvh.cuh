@@ -1,0 +1,262 @@
+// Per-world 4-wide BVH: leaf update, grow-only refit, top-down rebuild.
+//
+// Behavioural contract (reference CPU backend):
+//   BVH::updateLeafPosition / expandAABBWithMotion   M/src/physics/broadphase.cpp:440-485
+//   BVH::refitLeaf (grow-only min/max, stop when not expanded)   broadphase.cpp:550-647
+//   BVH::rebuild (two-level midpoint split, LIFO stack)          broadphase.cpp:47-285
+//   BVH::updateTree (rebuild only when forced by reset)           broadphase.cpp:649-656
+// Node / leaf records live in the world-major blob described in hs_state.cuh.
+#pragma once
+
+#include "hs_state.cuh"
+#include "hs_levelgen.cuh"   // c_assets
+
+namespace hs {
+
+__device__ __forceinline__ float *nodeF(uint32_t *blob, int n)
+{
+    return reinterpret_cast<float *>(blob + kBvhNodeOff + n * kNodeWords);
+}
+__device__ __forceinline__ int32_t *nodeI(uint32_t *blob, int n)
+{
+    return reinterpret_cast<int32_t *>(blob + kBvhNodeOff + n * kNodeWords);
+}
+__device__ __forceinline__ float *leafF(uint32_t *blob, int l)
+{
+    return reinterpret_cast<float *>(blob + kBvhLeafOff + l * kLeafWords);
+}
+__device__ __forceinline__ const float *nodeF(const uint32_t *blob, int n)
+{
+    return reinterpret_cast<const float *>(blob + kBvhNodeOff + n * kNodeWords);
+}
+__device__ __forceinline__ const int32_t *nodeI(const uint32_t *blob, int n)
+{
+    return reinterpret_cast<const int32_t *>(blob + kBvhNodeOff + n * kNodeWords);
+}
+__device__ __forceinline__ const float *leafF(const uint32_t *blob, int l)
+{
+    return reinterpret_cast<const float *>(blob + kBvhLeafOff + l * kLeafWords);
+}
+
+// updateLeafPositionsEntry: one thread per (slot, world), world fastest.
+__global__ void k_leaf_update(DeviceState S)
+{
+    const int N = S.p.numWorlds;
+    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)kMaxBodies * N) return;
+    int s = int(idx / N), w = int(idx % N);
+    if (s >= WI(S, WF_NUM_BODIES, w)) return;
+
+    uint32_t m = META(S, s, w);
+    Vec3 pos = loadPos(S, s, w);
+    Quat rot = loadRot(S, s, w);
+    Vec3 scale = loadScale(S, s, w);
+    Vec3 vel = loadV3(S, BF_VX, s, w);
+
+    AABB box = aabbApplyTRS(objAABB(metaObj(m)), pos, rot, scale);
+
+    // physics.cpp:104-111: velocity expansion 2*dt, accel expansion 100*dt*dt
+    const float vexp = 2.f * kDeltaT;
+    const float aexp = 100.f * kDeltaT * kDeltaT;
+    float lo[3] = {box.lo.x, box.lo.y, box.lo.z};
+    float hi[3] = {box.hi.x, box.hi.y, box.hi.z};
+    float v[3] = {vel.x, vel.y, vel.z};
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        float pd = vexp * v[i];
+        float mn = pd - aexp, mx = pd + aexp;
+        if (mn < 0.f) lo[i] += mn;
+        if (mx > 0.f) hi[i] += mx;
+    }
+
+    float *L = leafF(BVH(S, w), metaLeaf(m));
+    L[0] = lo[0]; L[1] = lo[1]; L[2] = lo[2];
+    L[3] = hi[0]; L[4] = hi[1]; L[5] = hi[2];
+    L[kLeafPos + 0] = pos.x; L[kLeafPos + 1] = pos.y; L[kLeafPos + 2] = pos.z;
+    L[kLeafRot + 0] = rot.w; L[kLeafRot + 1] = rot.x; L[kLeafRot + 2] = rot.y; L[kLeafRot + 3] = rot.z;
+    L[kLeafScale + 0] = scale.x; L[kLeafScale + 1] = scale.y; L[kLeafScale + 2] = scale.z;
+}
+
+__device__ __forceinline__ float atomicMinF(float *addr, float v)
+{
+    if (!signbit(v)) return __int_as_float(atomicMin((int *)addr, __float_as_int(v)));
+    return __uint_as_float(atomicMax((unsigned int *)addr, __float_as_uint(v)));
+}
+__device__ __forceinline__ float atomicMaxF(float *addr, float v)
+{
+    if (!signbit(v)) return __int_as_float(atomicMax((int *)addr, __float_as_int(v)));
+    return __uint_as_float(atomicMin((unsigned int *)addr, __float_as_uint(v)));
+}
+
+// refitEntry: one thread per (leaf, world).  min/max are exact and commutative,
+// and a node slot always encloses its subtree, so the result is independent of
+// the order leaves are processed in (sequential on the CPU).
+__global__ void k_refit(DeviceState S)
+{
+    const int N = S.p.numWorlds;
+    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)kMaxBodies * N) return;
+    int l = int(idx / N), w = int(idx % N);
+    uint32_t *blob = BVH(S, w);
+    if (l >= (int)blob[1]) return;
+
+    const float *L = leafF(blob, l);
+    float a[6] = {L[0], L[1], L[2], L[3], L[4], L[5]};
+    uint32_t lp = blob[kBvhLeafOff + l * kLeafWords + kLeafParent];
+    int node = int(lp >> 2), sub = int(lp & 3);
+
+    bool expanded = false;
+    {
+        float *nf = nodeF(blob, node);
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            float old = nf[k * 4 + sub];
+            if (a[k] < old) { nf[k * 4 + sub] = a[k]; expanded = true; }
+            float oldh = nf[(3 + k) * 4 + sub];
+            if (a[3 + k] > oldh) { nf[(3 + k) * 4 + sub] = a[3 + k]; expanded = true; }
+        }
+    }
+    if (!expanded) return;
+
+    int child = node;
+    node = nodeI(blob, node)[kNodeParent];
+    while (node != kSentinel) {
+        const int32_t *ni = nodeI(blob, node);
+        int off = 0;
+#pragma unroll
+        for (int j = 3; j >= 0; j--) if (ni[kNodeChild + j] == child) off = j;
+        float *nf = nodeF(blob, node);
+        bool ex = false;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            float old = atomicMinF(&nf[k * 4 + off], a[k]);
+            ex |= a[k] < old;
+            float oldh = atomicMaxF(&nf[(3 + k) * 4 + off], a[3 + k]);
+            ex |= a[3 + k] > oldh;
+        }
+        if (!ex) break;
+        child = node;
+        node = ni[kNodeParent];
+    }
+}
+
+// BVH::rebuild — one thread per world that has force_rebuild set.
+__global__ void k_bvh_rebuild(DeviceState S)
+{
+    int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= S.p.numWorlds) return;
+    uint32_t *blob = BVH(S, w);
+    if (blob[2] == 0) return;
+    blob[2] = 0;
+
+    const int numLeaves = (int)blob[1];
+    int tmp = numLeaves - 1;
+    int third = (tmp + 2) / 3;
+    blob[0] = uint32_t((third > 1 ? third : 1) + numLeaves);   // numInternalNodes
+
+    uint8_t sorted[kMaxBodies];
+    for (int i = 0; i < numLeaves; i++) sorted[i] = (uint8_t)i;
+
+    struct Entry { int nodeID, parentID, offset, numObjs; };
+    Entry stack[64];
+    stack[0] = {kSentinel, kSentinel, 0, numLeaves};
+    int stackSize = 1;
+    int curNode = 0;
+
+    auto center = [&](int leaf) {
+        const float *L = leafF(blob, leaf);
+        Vec3 lo = {L[0], L[1], L[2]}, hi = {L[3], L[4], L[5]};
+        return (lo + hi) * 0.5f;     // (pMin + pMax) / 2.f
+    };
+
+    auto midpointSplit = [&](int base, int n) {
+        Vec3 cmin = {FLT_MAX, FLT_MAX, FLT_MAX}, cmax = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+        for (int i = 0; i < n; i++) {
+            Vec3 c = center(sorted[base + i]);
+            cmin = vmin(cmin, c);
+            cmax = vmax(cmax, c);
+        }
+        Vec3 d = cmax - cmin;
+        int axis = (d.x > d.y && d.x > d.z) ? 0 : ((d.y > d.x && d.y > d.z) ? 1 : 2);
+        float splitVal = 0.5f * (comp(cmin, axis) + comp(cmax, axis));
+        int start = 0, end = n;
+        while (start < end) {
+            while (start < end && comp(center(sorted[base + start]), axis) < splitVal) ++start;
+            while (start < end && comp(center(sorted[base + end - 1]), axis) >= splitVal) --end;
+            if (start < end) {
+                uint8_t t = sorted[base + start];
+                sorted[base + start] = sorted[base + end - 1];
+                sorted[base + end - 1] = t;
+                ++start; --end;
+            }
+        }
+        return (start > 0 && start < n) ? start : n / 2;
+    };
+
+    while (stackSize > 0) {
+        Entry &e = stack[stackSize - 1];
+        int nodeId;
+        if (e.numObjs <= 4) {
+            nodeId = curNode++;
+            if (nodeId >= kMaxNodes) { atomicAdd(S.overflow, 1u); return; }
+            float *nf = nodeF(blob, nodeId);
+            int32_t *ni = nodeI(blob, nodeId);
+            ni[kNodeParent] = e.parentID;
+            for (int i = 0; i < 4; i++) {
+                if (i < e.numObjs) {
+                    int leaf = sorted[e.offset + i];
+                    const float *L = leafF(blob, leaf);
+                    blob[kBvhLeafOff + leaf * kLeafWords + kLeafParent] = (uint32_t(nodeId) << 2) | uint32_t(i);
+                    ni[kNodeChild + i] = int32_t(0x80000000u | uint32_t(leaf));
+                    for (int k = 0; k < 6; k++) nf[k * 4 + i] = L[k];
+                } else {
+                    ni[kNodeChild + i] = kSentinel;
+                    for (int k = 0; k < 3; k++) { nf[k * 4 + i] = FLT_MAX; nf[(3 + k) * 4 + i] = -FLT_MAX; }
+                }
+            }
+        } else if (e.nodeID == kSentinel) {
+            nodeId = curNode++;
+            if (nodeId >= kMaxNodes) { atomicAdd(S.overflow, 1u); return; }
+            e.nodeID = nodeId;
+            int32_t *ni = nodeI(blob, nodeId);
+            for (int i = 0; i < 4; i++) ni[kNodeChild + i] = kSentinel;
+            ni[kNodeParent] = e.parentID;
+
+            int second = midpointSplit(e.offset, e.numObjs);
+            int h1 = second, h2 = e.numObjs - second;
+            int first = midpointSplit(e.offset, h1);
+            int thirdS = midpointSplit(e.offset + second, h2);
+            int off = e.offset, self = e.nodeID;
+            stack[stackSize++] = {-1, self, off + h1 + thirdS, h2 - thirdS};
+            stack[stackSize++] = {-1, self, off + h1, thirdS};
+            stack[stackSize++] = {-1, self, off + first, h1 - first};
+            stack[stackSize++] = {-1, self, off, first};
+            continue;
+        } else {
+            nodeId = e.nodeID;
+        }
+
+        stackSize -= 1;
+        const int32_t *ni = nodeI(blob, nodeId);
+        int parent = ni[kNodeParent];
+        if (parent == -1) continue;
+
+        const float *nf = nodeF(blob, nodeId);
+        float c[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+        for (int i = 0; i < 4; i++) {
+            if (ni[kNodeChild + i] == kSentinel) break;
+            for (int k = 0; k < 3; k++) {
+                c[k] = fminf(c[k], nf[k * 4 + i]);
+                c[3 + k] = fmaxf(c[3 + k], nf[(3 + k) * 4 + i]);
+            }
+        }
+        int32_t *pi = nodeI(blob, parent);
+        float *pf = nodeF(blob, parent);
+        int off = 0;
+        while (pi[kNodeChild + off] != kSentinel) off++;
+        pi[kNodeChild + off] = nodeId;
+        for (int k = 0; k < 6; k++) pf[k * 4 + off] = c[k];
+    }
+}
+
+}  // namespace hs
