@@ -1,0 +1,97 @@
+/* hideseek B200 — C ABI of the CUDA batch simulator.
+ *
+ * This is the boundary the reference's `Manager` (src/mgr.hpp:14-99) is
+ * re-pointed at: where the reference holds a Madrona executor
+ * (CPU `TaskGraphExecutor` / GPU `MWCudaExecutor`, src/mgr.cpp:100-437) and asks
+ * it for `getExported(slot)` pointers (src/mgr.cpp:824-842), the drop-in holds an
+ * `hs_sim*` and calls the functions below.  Plain pointers and sizes only; no
+ * torch / nanobind types.  All functions return 0 on success, non-zero on
+ * failure with a message available from hs_last_error() (the reference aborts
+ * via FATAL/REQ_CUDA instead; the Manager layer turns errors back into aborts).
+ *
+ * One hs_sim owns one shard of worlds on one CUDA device.  Worlds are
+ * independent, so multi-GPU runs create one hs_sim per device with
+ * `world_base` set to the shard's first global world index (the episode RNG
+ * is keyed by global world index, src/sim.cpp:105-114).
+ */
+#ifndef HIDESEEK_C_API_H
+#define HIDESEEK_C_API_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hs_sim hs_sim;
+
+/* Mirrors Manager::Config (src/mgr.hpp:16-32); renderer fields are absent
+ * because the graphics path is unavailable on this box. */
+typedef struct hs_config {
+    int32_t gpu_id;
+    int32_t num_worlds;       /* worlds on this shard */
+    int32_t world_base;       /* global index of this shard's world 0 */
+    uint32_t sim_flags;       /* SimFlags bitmask, src/sim_flags.hpp:7-13 */
+    uint32_t rand_seed;
+    int32_t min_hiders, max_hiders;
+    int32_t min_seekers, max_seekers;
+    int32_t num_pbt_policies;
+} hs_config;
+
+/* ExportID numbering is the reference's (src/sim.hpp:45-68). */
+enum hs_export_id {
+    HS_EXPORT_RESET = 0, HS_EXPORT_PREP_COUNTER, HS_EXPORT_ACTION, HS_EXPORT_SELF_OBS,
+    HS_EXPORT_SELF_TYPE, HS_EXPORT_SELF_MASK, HS_EXPORT_AGENT_OBS, HS_EXPORT_BOX_OBS,
+    HS_EXPORT_RAMP_OBS, HS_EXPORT_AGENT_VIS, HS_EXPORT_BOX_VIS, HS_EXPORT_RAMP_VIS,
+    HS_EXPORT_LIDAR, HS_EXPORT_SEED, HS_EXPORT_REWARD, HS_EXPORT_DONE,
+    HS_EXPORT_GLOBAL_POS, HS_EXPORT_AGENT_POLICY, HS_EXPORT_EPISODE_RESULT,
+    HS_EXPORT_CKPT_CTRL, HS_EXPORT_CKPT, HS_NUM_EXPORTS
+};
+
+/* TensorElementType subset (M/include/madrona/py/utils.hpp) */
+enum hs_dtype { HS_U8 = 0, HS_I32 = 1, HS_F32 = 2 };
+
+/* Manager::Manager / ~Manager (src/mgr.cpp:844-859) */
+int hs_create(const hs_config *cfg, hs_sim **out);
+void hs_destroy(hs_sim *sim);
+
+/* Manager::init (src/mgr.cpp:861-881): runs the Init task graph
+ * (reset every world, build BVHs, first observations).  `stream` is a
+ * cudaStream_t (0 = legacy default stream); the call is asynchronous. */
+int hs_init(hs_sim *sim, void *stream);
+
+/* Manager::step (src/mgr.cpp:883-903): one 1/30 s tick of every world on
+ * `stream`, asynchronous.  hs_sync waits for it. */
+int hs_step(hs_sim *sim, void *stream);
+int hs_sync(hs_sim *sim, void *stream);
+
+/* Manager::*Tensor() getters (src/mgr.cpp:1062-1331): borrowed device pointer,
+ * stable until hs_destroy.  dims has room for 4 entries. */
+int hs_export(hs_sim *sim, int export_id, void **dev_ptr, int *dtype, int *ndim, int64_t *dims);
+
+/* Manager::triggerReset / setAction (src/mgr.cpp:1265-1310): host-side pokes,
+ * synchronous H2D writes like the reference's cudaMemcpy. */
+int hs_trigger_reset(hs_sim *sim, int world, int level);
+int hs_set_action(hs_sim *sim, int agent_row, int x, int y, int r, int g, int l);
+
+/* Host-buffer convenience used by the end-to-end path: copy a full action
+ * tensor [num_worlds*A,5] i32 from (pinned) host memory, step, and copy
+ * reward/done back.  Every copy is issued on `stream`. */
+int hs_step_host(hs_sim *sim, void *stream, const int32_t *actions_host,
+                 float *reward_host, int32_t *done_host);
+
+/* Diagnostics / parity: flat per-world internal state (layout in
+ * hideseek/debug_dump.h), number of kernels launched by the last hs_step,
+ * capacity-overflow counter. */
+int hs_dump_world(hs_sim *sim, int world, void *out, int out_bytes);
+int hs_world_dump_bytes(void);
+int hs_last_step_launches(hs_sim *sim);
+int hs_overflow_count(hs_sim *sim, uint32_t *out);
+
+const char *hs_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

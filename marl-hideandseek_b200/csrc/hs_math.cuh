@@ -8,6 +8,7 @@
 #pragma once
 
 #include <cfloat>
+#include <cmath>
 #include <cstdint>
 
 #if defined(__CUDACC__)

@@ -1,0 +1,361 @@
+// C-ABI entry points and the per-step launch sequence (include/hideseek/c_api.h).
+//
+// One translation unit so every kernel shares the __constant__ asset table.
+// The launch order is the node order of the reference's Step task graph
+// (src/sim.cpp:1140-1313).  There is no CPU fallback: every
+// entry point fails loudly if CUDA is unavailable.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <hideseek/c_api.h>
+#include <hideseek/debug_dump.h>
+
+#include "hs_state.cuh"
+#include "hs_rng.cuh"
+#include "hs_levelgen.cuh"
+#include "hs_bvh.cuh"
+#include "hs_trace.cuh"
+
+namespace hs {
+void buildAssetTable(AssetTable &T);
+}
+
+using namespace hs;
+
+static thread_local std::string g_err;
+
+#define HS_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { \
+    g_err = std::string(#x) + ": " + cudaGetErrorString(e_); return 1; } } while (0)
+
+struct hs_sim {
+    hs_config cfg;
+    DeviceState S;
+    std::vector<void *> allocs;
+    hs_world_dump *dumpDev = nullptr;
+    int lastLaunches = 0;
+    cudaGraphExec_t stepGraph = nullptr;
+    cudaStream_t graphStream = nullptr;
+    bool inited = false;
+};
+
+template <typename T>
+static int devAlloc(hs_sim *sim, T **out, size_t count)
+{
+    void *p = nullptr;
+    size_t bytes = count * sizeof(T);
+    if (bytes == 0) bytes = 16;
+    HS_CUDA(cudaMalloc(&p, bytes));
+    HS_CUDA(cudaMemset(p, 0, bytes));
+    sim->allocs.push_back(p);
+    *out = (T *)p;
+    return 0;
+}
+
+#define HS_TRY(x) do { if ((x) != 0) return 1; } while (0)
+
+extern "C" const char *hs_last_error(void) { return g_err.c_str(); }
+
+extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
+{
+    if (!cfg || !out) { g_err = "hs_create: null argument"; return 1; }
+    int A = cfg->max_hiders + cfg->max_seekers;
+    if (cfg->num_worlds <= 0 || A <= 0 || A > kMaxAgents || cfg->max_hiders > 3 || cfg->max_seekers > 3 ||
+        cfg->min_hiders > cfg->max_hiders || cfg->min_seekers > cfg->max_seekers) {
+        g_err = "hs_create: invalid configuration";
+        return 1;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        g_err = "hs_create: no CUDA device (this library has no CPU fallback)";
+        return 1;
+    }
+    HS_CUDA(cudaSetDevice(cfg->gpu_id));
+
+    hs_sim *sim = new hs_sim();
+    sim->cfg = *cfg;
+    DeviceState &S = sim->S;
+    const size_t N = (size_t)cfg->num_worlds;
+    RandKey ik = initKey(cfg->rand_seed);
+    S.p = SimParams{cfg->num_worlds, cfg->world_base, A, cfg->sim_flags, ik.a, ik.b,
+                    cfg->min_hiders, cfg->max_hiders, cfg->min_seekers, cfg->max_seekers};
+
+    HS_TRY(devAlloc(sim, &S.body, size_t(BF_COUNT) * kMaxBodies * N));
+    HS_TRY(devAlloc(sim, &S.meta, size_t(kMaxBodies) * N));
+    HS_TRY(devAlloc(sim, &S.wi, size_t(WF_COUNT) * N));
+    HS_TRY(devAlloc(sim, &S.wb, size_t(WB_COUNT) * N));
+    HS_TRY(devAlloc(sim, &S.joint, size_t(JF_COUNT) * kMaxAgents * N));
+    HS_TRY(devAlloc(sim, &S.jmeta, size_t(kMaxAgents) * N));
+    HS_TRY(devAlloc(sim, &S.bvh, size_t(kBvhWords) * N));
+    HS_TRY(devAlloc(sim, &S.cand, size_t(kMaxCand) * N));
+    HS_TRY(devAlloc(sim, &S.contact, size_t(kMaxCand) * kContactWords * N));
+    HS_TRY(devAlloc(sim, &S.cmeta, size_t(kMaxCand) * N));
+    HS_TRY(devAlloc(sim, &S.overflow, 4));
+
+    const size_t R = N * A;
+    HS_TRY(devAlloc(sim, &S.exReset, N));
+    HS_TRY(devAlloc(sim, &S.exPrepCounter, R));
+    HS_TRY(devAlloc(sim, &S.exAction, R * 5));
+    HS_TRY(devAlloc(sim, &S.exSelfObs, R * 13));
+    HS_TRY(devAlloc(sim, &S.exSelfType, R));
+    HS_TRY(devAlloc(sim, &S.exSelfMask, R));
+    HS_TRY(devAlloc(sim, &S.exAgentObs, R * 5 * 14));
+    HS_TRY(devAlloc(sim, &S.exBoxObs, R * 9 * 17));
+    HS_TRY(devAlloc(sim, &S.exRampObs, R * 2 * 14));
+    HS_TRY(devAlloc(sim, &S.exAgentVis, R * 5));
+    HS_TRY(devAlloc(sim, &S.exBoxVis, R * 9));
+    HS_TRY(devAlloc(sim, &S.exRampVis, R * 2));
+    HS_TRY(devAlloc(sim, &S.exLidar, R * 30));
+    HS_TRY(devAlloc(sim, &S.exSeed, R * 2));
+    HS_TRY(devAlloc(sim, &S.exReward, R));
+    HS_TRY(devAlloc(sim, &S.exDone, R));
+    HS_TRY(devAlloc(sim, &S.exGlobalPos, N * 17 * 2));
+    HS_TRY(devAlloc(sim, &S.exPolicy, R));
+    HS_TRY(devAlloc(sim, &S.exEpisodeResult, N * 2));
+    HS_TRY(devAlloc(sim, &S.exCkptCtrl, N));
+    HS_TRY(devAlloc(sim, &S.exCkpt, N * kCheckpointBytes));
+    HS_TRY(devAlloc(sim, &sim->dumpDev, 1));
+
+    AssetTable T;
+    buildAssetTable(T);
+    HS_CUDA(cudaMemcpyToSymbol(c_assets, &T, sizeof(T)));
+
+    HS_CUDA(cudaStreamCreateWithFlags(&sim->graphStream, cudaStreamNonBlocking));
+    *out = sim;
+    return 0;
+}
+
+extern "C" void hs_destroy(hs_sim *sim)
+{
+    if (!sim) return;
+    cudaSetDevice(sim->cfg.gpu_id);
+    cudaDeviceSynchronize();
+    if (sim->stepGraph) cudaGraphExecDestroy(sim->stepGraph);
+    if (sim->graphStream) cudaStreamDestroy(sim->graphStream);
+    for (void *p : sim->allocs) cudaFree(p);
+    delete sim;
+}
+
+// ---- construction-time world state (Sim::Sim, src/sim.cpp:1346-1408) ----------
+__global__ void k_world_init(DeviceState S)
+{
+    int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= S.p.numWorlds) return;
+    WI(S, WF_ID_FRESH, w) = S.p.agentsPerWorld;   // interface entities took the first ids
+    WI(S, WF_HIDER_REWARD, w) = __float_as_int(1.f);
+    for (int k = 0; k < kMaxAgents; k++) {
+        JMETA(S, k, w) = 0xFFFFFFFFu;
+        WB(S, WB_IFACE_SLOT + k, w) = 0xFF;
+    }
+    S.exReset[w] = 1;                              // resetLevel = 1 in the constructor
+    BVH(S, w)[2] = 1;                              // BVH ctor: force_rebuild_ = true
+}
+
+__global__ void k_dump_world(DeviceState S, int w, hs_world_dump *out)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    hs_world_dump &d = *out;
+    d.cur_episode_step = WI(S, WF_EPISODE_STEP, w);
+    d.cur_world_episode = WI(S, WF_WORLD_EPISODE, w);
+    d.episode_key[0] = WI(S, WF_EP_KEY_A, w); d.episode_key[1] = WI(S, WF_EP_KEY_B, w);
+    d.rng_key[0] = WI(S, WF_RNG_A, w); d.rng_key[1] = WI(S, WF_RNG_B, w);
+    d.rng_count = WI(S, WF_RNG_COUNT, w);
+    d.num_hiders = WI(S, WF_NUM_HIDERS, w); d.num_seekers = WI(S, WF_NUM_SEEKERS, w);
+    d.num_agents = WI(S, WF_NUM_AGENTS, w);
+    d.num_dyn = WI(S, WF_NUM_DYN, w); d.num_bodies = WI(S, WF_NUM_BODIES, w);
+    d.num_boxes = WI(S, WF_NUM_BOXES, w); d.num_ramps = WI(S, WF_NUM_RAMPS, w);
+    d.hider_team_reward = __int_as_float(WI(S, WF_HIDER_REWARD, w));
+    d.seekers_first = WI(S, WF_SEEKERS_FIRST, w);
+    d.running_scores[0] = WI(S, WF_SCORE0, w); d.running_scores[1] = WI(S, WF_SCORE1, w);
+    d.num_cand = WI(S, WF_NUM_CAND, w);
+    for (int i = 0; i < 9; i++) d.box_slot[i] = WB(S, WB_BOX_SLOT + i, w);
+    for (int i = 0; i < 2; i++) d.ramp_slot[i] = WB(S, WB_RAMP_SLOT + i, w);
+    for (int i = 0; i < 3; i++) { d.hider_slot[i] = WB(S, WB_HIDER_SLOT + i, w); d.seeker_slot[i] = WB(S, WB_SEEKER_SLOT + i, w); }
+    for (int i = 0; i < kMaxAgents; i++) {
+        int s = WB(S, WB_IFACE_SLOT + i, w);
+        d.iface_slot[i] = s == 0xFF ? -1 : s;
+        d.iface_type[i] = WB(S, WB_IFACE_TYPE + i, w);
+    }
+    for (int s = 0; s < kMaxBodies; s++) {
+        hs_dump_body &b = d.bodies[s];
+        uint32_t m = META(S, s, w);
+        b.eid = metaEid(m); b.obj = metaObj(m); b.response = metaResp(m);
+        b.owner = metaOwner(m); b.leaf = metaLeaf(m);
+        for (int k = 0; k < 3; k++) b.pos[k] = BF(S, BF_PX + k, s, w);
+        for (int k = 0; k < 4; k++) b.rot[k] = BF(S, BF_QW + k, s, w);
+        for (int k = 0; k < 3; k++) b.scale[k] = BF(S, BF_SX + k, s, w);
+        for (int k = 0; k < 6; k++) b.vel[k] = BF(S, BF_VX + k, s, w);
+        for (int k = 0; k < 3; k++) b.ext_force[k] = BF(S, BF_FX + k, s, w);
+        for (int k = 0; k < 3; k++) b.ext_torque[k] = BF(S, BF_TX + k, s, w);
+    }
+    for (int k = 0; k < kMaxAgents; k++) {
+        hs_dump_joint &j = d.joints[k];
+        uint32_t jm = JMETA(S, k, w);
+        j.active = jm != 0xFFFFFFFFu;
+        j.other_slot = jm & 0xFF; j.eid = (jm >> 8) & 0xFF; j.seq = jm >> 16;
+        for (int c = 0; c < 4; c++) { j.attach1[c] = JF(S, JF_A1W + c, k, w); j.attach2[c] = JF(S, JF_A2W + c, k, w); }
+        j.separation = JF(S, JF_SEP, k, w);
+        for (int c = 0; c < 3; c++) { j.r1[c] = JF(S, JF_R1X + c, k, w); j.r2[c] = JF(S, JF_R2X + c, k, w); }
+    }
+    const uint32_t *blob = BVH(S, w);
+    d.bvh_num_nodes = blob[0]; d.bvh_num_leaves = blob[1]; d.bvh_force_rebuild = blob[2];
+    for (int n = 0; n < kMaxNodes; n++) {
+        const float *nf = nodeF(blob, n);
+        const int32_t *ni = nodeI(blob, n);
+        for (int k = 0; k < 24; k++) d.nodes[n].bounds[k] = nf[k];
+        for (int k = 0; k < 4; k++) d.nodes[n].children[k] = ni[kNodeChild + k];
+        d.nodes[n].parent = ni[kNodeParent];
+    }
+    for (int l = 0; l < kMaxBodies; l++) {
+        const float *L = leafF(blob, l);
+        for (int k = 0; k < 6; k++) d.leaf_aabbs[l][k] = L[k];
+        d.leaf_parents[l] = blob[kBvhLeafOff + l * kLeafWords + kLeafParent];
+        d.leaf_slot[l] = blob[kBvhLeafOff + l * kLeafWords + kLeafInfo] & 0xFF;
+    }
+    for (int c = 0; c < kMaxCand; c++) {
+        uint16_t v = S.cand[size_t(w) * kMaxCand + c];
+        d.cand_a[c] = v & 0xFF; d.cand_b[c] = v >> 8;
+        d.contact_meta[c] = S.cmeta[size_t(w) * kMaxCand + c];
+        for (int k = 0; k < kContactWords; k++)
+            d.contacts[c][k] = S.contact[(size_t(w) * kMaxCand + c) * kContactWords + k];
+    }
+}
+
+extern "C" int hs_world_dump_bytes(void) { return (int)sizeof(hs_world_dump); }
+
+extern "C" int hs_dump_world(hs_sim *sim, int world, void *out, int out_bytes)
+{
+    if (!sim || world < 0 || world >= sim->cfg.num_worlds || out_bytes < (int)sizeof(hs_world_dump)) {
+        g_err = "hs_dump_world: bad argument";
+        return 1;
+    }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    HS_CUDA(cudaDeviceSynchronize());
+    k_dump_world<<<1, 1>>>(sim->S, world, sim->dumpDev);
+    HS_CUDA(cudaGetLastError());
+    HS_CUDA(cudaMemcpy(out, sim->dumpDev, sizeof(hs_world_dump), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int hs_overflow_count(hs_sim *sim, uint32_t *out)
+{
+    HS_CUDA(cudaMemcpy(out, sim->S.overflow, 4, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int hs_last_step_launches(hs_sim *sim) { return sim->lastLaunches; }
+
+// ---- launch sequence ------------------------------------------------------------
+namespace {
+
+struct Launcher {
+    const DeviceState &S;
+    cudaStream_t st;
+    int count = 0;
+    int N() const { return S.p.numWorlds; }
+    // thread per world
+    dim3 gWorld(int block = 128) const { return dim3((N() + block - 1) / block); }
+    // thread per (slot, world)
+    dim3 gBody(int block = 256) const { return dim3(unsigned(((long long)kMaxBodies * N() + block - 1) / block)); }
+    // warp per world
+    dim3 gWarpWorld(int block = 128) const { return dim3(unsigned(((long long)N() * 32 + block - 1) / block)); }
+    // thread per agent row
+    dim3 gAgent(int block = 128) const { return dim3((N() * S.p.agentsPerWorld + block - 1) / block); }
+    // warp per agent row
+    dim3 gWarpAgent(int block = 128) const { return dim3(unsigned(((long long)N() * S.p.agentsPerWorld * 32 + block - 1) / block)); }
+};
+
+// setupBVHTasks (broadphase.cpp:995-1017): update leaves, rebuild if forced, refit
+void launchBroadphaseSetup(Launcher &L, bool mayRebuild)
+{
+    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+    if (mayRebuild) { k_bvh_rebuild<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++; }
+    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+}
+
+void launchObservations(Launcher &L);
+void launchStep(Launcher &L);
+
+}  // namespace
+
+extern "C" int hs_init(hs_sim *sim, void *stream)
+{
+    if (!sim) { g_err = "hs_init: null sim"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    Launcher L{sim->S, (cudaStream_t)stream};
+    k_world_init<<<L.gWorld(), 128, 0, L.st>>>(L.S);
+    // Init task graph (src/sim.cpp:1295-1305): reset -> broadphase setup -> observations
+    k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S);
+    launchBroadphaseSetup(L, true);
+    launchObservations(L);
+    HS_CUDA(cudaGetLastError());
+    sim->inited = true;
+    return 0;
+}
+
+extern "C" int hs_sync(hs_sim *sim, void *stream)
+{
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    HS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int hs_export(hs_sim *sim, int id, void **ptr, int *dtype, int *ndim, int64_t *dims)
+{
+    if (!sim || !ptr || !dtype || !ndim || !dims) { g_err = "hs_export: null argument"; return 1; }
+    const DeviceState &S = sim->S;
+    const int64_t N = S.p.numWorlds, R = N * S.p.agentsPerWorld;
+    auto set = [&](void *p, int dt, int nd, int64_t d0, int64_t d1, int64_t d2) {
+        *ptr = p; *dtype = dt; *ndim = nd; dims[0] = d0; dims[1] = d1; dims[2] = d2; dims[3] = 0;
+    };
+    // shapes: src/mgr.cpp:1062-1331
+    switch (id) {
+    case HS_EXPORT_RESET: set(S.exReset, HS_I32, 2, N, 1, 0); break;
+    case HS_EXPORT_PREP_COUNTER: set(S.exPrepCounter, HS_I32, 2, R, 1, 0); break;
+    case HS_EXPORT_ACTION: set(S.exAction, HS_I32, 2, R, 5, 0); break;
+    case HS_EXPORT_SELF_OBS: set(S.exSelfObs, HS_F32, 2, R, 13, 0); break;
+    case HS_EXPORT_SELF_TYPE: set(S.exSelfType, HS_I32, 2, R, 1, 0); break;
+    case HS_EXPORT_SELF_MASK: set(S.exSelfMask, HS_F32, 2, R, 1, 0); break;
+    case HS_EXPORT_AGENT_OBS: set(S.exAgentObs, HS_F32, 3, R, 5, 14); break;
+    case HS_EXPORT_BOX_OBS: set(S.exBoxObs, HS_F32, 3, R, 9, 17); break;
+    case HS_EXPORT_RAMP_OBS: set(S.exRampObs, HS_F32, 3, R, 2, 14); break;
+    case HS_EXPORT_AGENT_VIS: set(S.exAgentVis, HS_F32, 3, R, 5, 1); break;
+    case HS_EXPORT_BOX_VIS: set(S.exBoxVis, HS_F32, 3, R, 9, 1); break;
+    case HS_EXPORT_RAMP_VIS: set(S.exRampVis, HS_F32, 3, R, 2, 1); break;
+    case HS_EXPORT_LIDAR: set(S.exLidar, HS_F32, 2, R, 30, 0); break;
+    case HS_EXPORT_SEED: set(S.exSeed, HS_I32, 2, R, 2, 0); break;
+    case HS_EXPORT_REWARD: set(S.exReward, HS_F32, 2, R, 1, 0); break;
+    case HS_EXPORT_DONE: set(S.exDone, HS_I32, 2, R, 1, 0); break;
+    case HS_EXPORT_GLOBAL_POS: set(S.exGlobalPos, HS_F32, 3, N, 17, 2); break;
+    case HS_EXPORT_AGENT_POLICY: set(S.exPolicy, HS_I32, 2, R, 1, 0); break;
+    case HS_EXPORT_EPISODE_RESULT: set(S.exEpisodeResult, HS_F32, 2, N, 2, 0); break;
+    case HS_EXPORT_CKPT_CTRL: set(S.exCkptCtrl, HS_I32, 2, N, 1, 0); break;
+    case HS_EXPORT_CKPT: set(S.exCkpt, HS_U8, 2, N, kCheckpointBytes, 0); break;
+    default: g_err = "hs_export: unknown export id"; return 1;
+    }
+    return 0;
+}
+
+extern "C" int hs_trigger_reset(hs_sim *sim, int world, int level)
+{
+    if (!sim || world < 0 || world >= sim->cfg.num_worlds) { g_err = "hs_trigger_reset: bad world"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    int32_t v = level;
+    HS_CUDA(cudaMemcpy(sim->S.exReset + world, &v, 4, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" int hs_set_action(hs_sim *sim, int row, int x, int y, int r, int g, int l)
+{
+    if (!sim || row < 0 || row >= sim->cfg.num_worlds * sim->S.p.agentsPerWorld) {
+        g_err = "hs_set_action: bad agent row";
+        return 1;
+    }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    int32_t a[5] = {x, y, r, g ? 1 : 0, l ? 1 : 0};
+    HS_CUDA(cudaMemcpy(sim->S.exAction + size_t(row) * 5, a, sizeof(a), cudaMemcpyHostToDevice));
+    return 0;
+}

@@ -26,6 +26,7 @@ constexpr int kMaxWalls = 33;      // src/geo_gen.cpp:145,430-433
 constexpr int kMaxNodes = 69;      // BVH::numInternalNodes(52), broadphase.cpp:38-45
 constexpr int kMaxCand = 256;
 constexpr int kIdPool = 64;        // ids_per_cache_ (id_map.hpp)
+constexpr int kCheckpointBytes = 1392;   // sizeof(Checkpoint), src/sim.hpp:283-313
 
 constexpr float kDeltaT = 1.f / 30.f;       // src/sim.cpp:14
 constexpr int kSubsteps = 4;
