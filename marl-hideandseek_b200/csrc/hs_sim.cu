@@ -19,6 +19,10 @@
 #include "hs_levelgen.cuh"
 #include "hs_bvh.cuh"
 #include "hs_trace.cuh"
+#include "hs_agents.cuh"
+#include "hs_obs.cuh"
+#include "hs_narrowphase.cuh"
+#include "hs_solver.cuh"
 
 namespace hs {
 void buildAssetTable(AssetTable &T);
@@ -40,6 +44,7 @@ struct hs_sim {
     cudaGraphExec_t stepGraph = nullptr;
     cudaStream_t graphStream = nullptr;
     bool inited = false;
+    float cosThreshold = 0.f;
 };
 
 template <typename T>
@@ -124,6 +129,12 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     HS_CUDA(cudaMemcpyToSymbol(c_assets, &T, sizeof(T)));
 
     HS_CUDA(cudaStreamCreateWithFlags(&sim->graphStream, cudaStreamNonBlocking));
+    {
+        // cosf(toRadians(135.f / 2.f)) as the reference's compiler folds it (src/sim.cpp:582,767)
+        float mult = 3.14159265358979323846f / 180.f;
+        float ang = mult * (135.f / 2.f);
+        sim->cosThreshold = (float)cos((double)ang);
+    }
     *out = sim;
     return 0;
 }
@@ -276,8 +287,39 @@ void launchBroadphaseSetup(Launcher &L, bool mayRebuild)
     k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
 }
 
-void launchObservations(Launcher &L);
-void launchStep(Launcher &L);
+// observationsTasks (src/sim.cpp:1232-1293)
+void launchObservations(Launcher &L, float cosThr)
+{
+    k_observations<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.count++;
+    k_visibility<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S, cosThr); L.count++;
+    k_lidar<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.count++;
+    k_debug_positions<<<L.gWorld(), 128, 0, L.st>>>(L.S); L.count++;
+}
+
+// Step task graph (src/sim.cpp:1307-1313), node order of SURVEY.md §3.3
+void launchStep(Launcher &L, float cosThr)
+{
+    k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.count++;
+    launchBroadphaseSetup(L, true);
+    k_action<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
+    k_broadphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.count++;
+    for (int i = 0; i < kSubsteps; i++) {
+        k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+        k_narrowphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.count++;
+        k_solve_positions<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
+        k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+        k_solve_velocities<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
+    }
+    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+    if (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) {
+        k_zero_agent_vel<<<dim3((L.N() * kMaxAgents + 127) / 128), 128, 0, L.st>>>(L.S); L.count++;
+    }
+    k_rewards<<<L.gWorld(64), 64, 0, L.st>>>(L.S, cosThr); L.count++;
+    k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
+    launchBroadphaseSetup(L, true);
+    launchObservations(L, cosThr);
+}
 
 }  // namespace
 
@@ -290,7 +332,7 @@ extern "C" int hs_init(hs_sim *sim, void *stream)
     // Init task graph (src/sim.cpp:1295-1305): reset -> broadphase setup -> observations
     k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S);
     launchBroadphaseSetup(L, true);
-    launchObservations(L);
+    launchObservations(L, sim->cosThreshold);
     HS_CUDA(cudaGetLastError());
     sim->inited = true;
     return 0;
@@ -357,5 +399,42 @@ extern "C" int hs_set_action(hs_sim *sim, int row, int x, int y, int r, int g, i
     HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
     int32_t a[5] = {x, y, r, g ? 1 : 0, l ? 1 : 0};
     HS_CUDA(cudaMemcpy(sim->S.exAction + size_t(row) * 5, a, sizeof(a), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" int hs_step(hs_sim *sim, void *stream)
+{
+    if (!sim || !sim->inited) { g_err = "hs_step: hs_init has not run"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!sim->stepGraph) {
+        // capture the step once on a private stream; replay on the caller's stream
+        cudaGraph_t graph;
+        HS_CUDA(cudaStreamBeginCapture(sim->graphStream, cudaStreamCaptureModeThreadLocal));
+        Launcher L{sim->S, sim->graphStream};
+        launchStep(L, sim->cosThreshold);
+        HS_CUDA(cudaStreamEndCapture(sim->graphStream, &graph));
+        HS_CUDA(cudaGraphInstantiate(&sim->stepGraph, graph, 0));
+        HS_CUDA(cudaGraphDestroy(graph));
+        sim->lastLaunches = L.count;
+    }
+    HS_CUDA(cudaGraphLaunch(sim->stepGraph, st));
+    return 0;
+}
+
+extern "C" int hs_step_host(hs_sim *sim, void *stream, const int32_t *actions_host,
+                            float *reward_host, int32_t *done_host)
+{
+    if (!sim) { g_err = "hs_step_host: null sim"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    cudaStream_t st = (cudaStream_t)stream;
+    size_t R = size_t(sim->cfg.num_worlds) * sim->S.p.agentsPerWorld;
+    if (actions_host)
+        HS_CUDA(cudaMemcpyAsync(sim->S.exAction, actions_host, R * 5 * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    HS_TRY(hs_step(sim, stream));
+    if (reward_host)
+        HS_CUDA(cudaMemcpyAsync(reward_host, sim->S.exReward, R * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (done_host)
+        HS_CUDA(cudaMemcpyAsync(done_host, sim->S.exDone, R * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     return 0;
 }

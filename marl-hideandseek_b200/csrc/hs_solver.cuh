@@ -1,0 +1,420 @@
+// XPBD rigid-body solver: substep integration, sequential position solve over
+// contacts then joints, velocity derivation, restitution + dynamic friction.
+//
+// Behavioural contract (M/src/physics/xpbd.cpp):
+//   substepRigidBodies 100-185 · computePositionalLambda / applyPositionalUpdate 206-285
+//   computeAngularUpdate / applyAngularUpdate 287-319 · handleContactConstraint 321-403
+//   getLocalSpaceContacts / getAvgContact / handleContact 405-550
+//   applyJointOrientationConstraint / handleJointConstraint (Fixed) 552-718
+//   solvePositions 720-736 · setVelocities 738-779
+//   applyFrictionVelocityUpdate / applyRestitutionVelocityUpdate /
+//   solveVelocitiesForContact / solveVelocities 781-1052
+// Gauss-Seidel order = contact creation order, then joints in creation order
+// (SURVEY.md App. B-6), so the position/velocity solves run one thread per world.
+#pragma once
+
+#include "hs_narrowphase.cuh"
+
+namespace hs {
+
+__device__ __forceinline__ float substepH() { return kDeltaT / float(kSubsteps); }
+
+// one thread per (slot, world)
+__global__ void k_substep(DeviceState S)
+{
+    const int N = S.p.numWorlds;
+    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)kMaxBodies * N) return;
+    int s = int(idx / N), w = int(idx % N);
+    if (s >= WI(S, WF_NUM_BODIES, w)) return;
+
+    uint32_t m = META(S, s, w);
+    Vec3 x = loadPos(S, s, w);
+    Quat q = loadRot(S, s, w);
+    storeV3(S, BF_PREV_PX, s, w, x);
+    storeQ(S, BF_PREV_QW, s, w, q);
+
+    if (metaResp(m) == RESP_STATIC) {
+        storeV3(S, BF_PRE_PX, s, w, x);
+        storeQ(S, BF_PRE_QW, s, w, q);
+        storeV3(S, BF_PRE_VX, s, w, {0.f, 0.f, 0.f});
+        storeV3(S, BF_PRE_WX, s, w, {0.f, 0.f, 0.f});
+        return;
+    }
+
+    Vec3 v = loadV3(S, BF_VX, s, w);
+    Vec3 omega = loadV3(S, BF_WX, s, w);
+    const ObjectData &O = c_assets.obj[metaObj(m)];
+    float inv_m = O.invMass;
+    Vec3 inv_I = {O.invInertia[0], O.invInertia[1], O.invInertia[2]};
+    const float h = substepH();
+
+    if (metaResp(m) == RESP_DYNAMIC) {
+        const Vec3 g = -9.8f * v3(0, 0, 1);
+        v += h * g;
+    }
+    v += (h * inv_m) * loadV3(S, BF_FX, s, w);
+    x += h * v;
+
+    Vec3 I = {inv_I.x == 0 ? 0.0f : 1.0f / inv_I.x,
+              inv_I.y == 0 ? 0.0f : 1.0f / inv_I.y,
+              inv_I.z == 0 ? 0.0f : 1.0f / inv_I.z};
+    Quat toLocal = qinv(q);
+    Vec3 tauLocal = rotate(toLocal, loadV3(S, BF_TX, s, w));
+    Vec3 omegaLocal = rotate(toLocal, omega);
+    Vec3 IOmega = mulDiag(I, omegaLocal);
+    omegaLocal += h * mulDiag(inv_I, tauLocal - cross(omegaLocal, IOmega));
+    omega = rotate(q, omegaLocal);
+
+    Quat applyOmega = fromAngularVec((0.5f * h) * omega);
+    q = q + applyOmega * q;
+    q = qnormalize(q);
+
+    storeV3(S, BF_PX, s, w, x);
+    storeQ(S, BF_QW, s, w, q);
+    storeV3(S, BF_PRE_PX, s, w, x);
+    storeQ(S, BF_PRE_QW, s, w, q);
+    storeV3(S, BF_PRE_VX, s, w, v);
+    storeV3(S, BF_PRE_WX, s, w, omega);
+}
+
+struct MassData { float inv_m; Vec3 inv_I; float muS, muD; };
+
+__device__ __forceinline__ MassData massOf(uint32_t meta)
+{
+    const ObjectData &O = c_assets.obj[metaObj(meta)];
+    MassData d = {O.invMass, {O.invInertia[0], O.invInertia[1], O.invInertia[2]}, O.muS, O.muD};
+    if (metaResp(meta) == RESP_STATIC) { d.inv_m = 0.f; d.inv_I = {0.f, 0.f, 0.f}; }
+    return d;
+}
+
+__device__ __forceinline__ float positionalLambda(Vec3 ta1, Vec3 ta2, Vec3 ra1, Vec3 ra2,
+                                                  float inv_m1, float inv_m2, float c, float alpha)
+{
+    float w1 = inv_m1 + dot(ta1, ra1);
+    float w2 = inv_m2 + dot(ta2, ra2);
+    return -c / (w1 + w2 + alpha);
+}
+
+__device__ __forceinline__ void applyPositional(Vec3 &x1, Vec3 &x2, Quat &q1, Quat &q2,
+                                                Vec3 ra1, Vec3 ra2, float inv_m1, float inv_m2,
+                                                Vec3 n, float lambda)
+{
+    x1 += (lambda * inv_m1) * n;
+    x2 -= (lambda * inv_m2) * n;
+    float half = 0.5f * lambda;
+    Vec3 u1 = rotate(q1, half * ra1);
+    Vec3 u2 = rotate(q2, half * ra2);
+    q1 = q1 + fromAngularVec(u1) * q1;
+    q2 = q2 - fromAngularVec(u2) * q2;
+    q1 = qnormalize(q1);
+    q2 = qnormalize(q2);
+}
+
+__device__ __forceinline__ float applyPositionalFull(Vec3 &x1, Vec3 &x2, Quat &q1, Quat &q2,
+                                                     Vec3 r1, Vec3 r2, const MassData &m1, const MassData &m2,
+                                                     Vec3 n, float c, float alpha)
+{
+    Vec3 n1 = rotate(qinv(q1), n), n2 = rotate(qinv(q2), n);
+    Vec3 ta1 = cross(r1, n1), ta2 = cross(r2, n2);
+    Vec3 ra1 = mulDiag(m1.inv_I, ta1), ra2 = mulDiag(m2.inv_I, ta2);
+    float lambda = positionalLambda(ta1, ta2, ra1, ra2, m1.inv_m, m2.inv_m, c, alpha);
+    applyPositional(x1, x2, q1, q2, ra1, ra2, m1.inv_m, m2.inv_m, n, lambda);
+    return lambda;
+}
+
+struct ContactView {
+    Vec3 pts[4];
+    float depth[4];
+    int n;
+    Vec3 normal;
+};
+
+__device__ __forceinline__ ContactView loadContact(const float *c, uint32_t meta)
+{
+    ContactView v;
+    for (int i = 0; i < 4; i++) {
+        v.pts[i] = {c[i * 4], c[i * 4 + 1], c[i * 4 + 2]};
+        v.depth[i] = c[i * 4 + 3];
+    }
+    v.n = int(meta >> 16) & 0xFF;
+    v.normal = {c[16], c[17], c[18]};
+    return v;
+}
+
+// getAvgContact: returns true when the contact has zero total penetration
+__device__ __forceinline__ bool avgContact(const ContactView &c, Vec3 *avg, float *pen)
+{
+    float maxPen = -FLT_MAX, sum = 0.f;
+    for (int i = 0; i < c.n; i++) {
+        if (c.depth[i] > maxPen) maxPen = c.depth[i];
+        sum += c.depth[i];
+    }
+    if (sum == 0.f) return true;
+    Vec3 a = {0.f, 0.f, 0.f};
+    for (int i = 0; i < c.n; i++) a += (c.depth[i] / sum) * c.pts[i];
+    *avg = a;
+    *pen = maxPen;
+    return false;
+}
+
+__device__ __forceinline__ void localContacts(Vec3 px1, Quat pq1, Vec3 px2, Quat pq2,
+                                              Vec3 contact1, float pen, Vec3 normal, Vec3 *r1, Vec3 *r2)
+{
+    Vec3 contact2 = contact1 - normal * pen;
+    *r1 = rotate(qinv(pq1), contact1 - px1);
+    *r2 = rotate(qinv(pq2), contact2 - px2);
+}
+
+__device__ inline void handleContact(const DeviceState &S, int w, uint32_t meta, float *cdata)
+{
+    const int b1 = meta & 0xFF, b2 = (meta >> 8) & 0xFF;
+    ContactView c = loadContact(cdata, meta);
+    MassData m1 = massOf(META(S, b1, w)), m2 = massOf(META(S, b2, w));
+    float avgMuS = 0.5f * (m1.muS + m2.muS);
+
+    Vec3 avg; float pen;
+    if (avgContact(c, &avg, &pen)) return;
+
+    Vec3 x1 = loadPos(S, b1, w), x2 = loadPos(S, b2, w);
+    Quat q1 = loadRot(S, b1, w), q2 = loadRot(S, b2, w);
+    Vec3 r1, r2;
+    localContacts(loadV3(S, BF_PRE_PX, b1, w), loadQ(S, BF_PRE_QW, b1, w),
+                  loadV3(S, BF_PRE_PX, b2, w), loadQ(S, BF_PRE_QW, b2, w),
+                  avg, pen, c.normal, &r1, &r2);
+
+    // handleContactConstraint
+    Vec3 n = c.normal;
+    Vec3 p1 = rotate(q1, r1) + x1, p2 = rotate(q2, r2) + x2;
+    float d = dot(p1 - p2, n);
+    float lambda_n = 0.f;
+    if (d > 0) {
+        lambda_n = applyPositionalFull(x1, x2, q1, q2, r1, r2, m1, m2, n, d, 0.f);
+
+        Vec3 p1_hat = rotate(loadQ(S, BF_PREV_QW, b1, w), r1) + loadV3(S, BF_PREV_PX, b1, w);
+        Vec3 p2_hat = rotate(loadQ(S, BF_PREV_QW, b2, w), r2) + loadV3(S, BF_PREV_PX, b2, w);
+        p1 = rotate(q1, r1) + x1;
+        p2 = rotate(q2, r2) + x2;
+        Vec3 dp = (p1 - p1_hat) - (p2 - p2_hat);
+        Vec3 dpt = dp - dot(dp, n) * n;
+        float tmag = length(dpt);
+        if (tmag > 0.f) {
+            Vec3 t = dpt / tmag;
+            Vec3 t1 = rotate(qinv(q1), t), t2 = rotate(qinv(q2), t);
+            Vec3 fa1 = cross(r1, t1), fa2 = cross(r2, t2);
+            Vec3 fr1 = mulDiag(m1.inv_I, fa1), fr2 = mulDiag(m2.inv_I, fa2);
+            float lambda_t = positionalLambda(fa1, fa2, fr1, fr2, m1.inv_m, m2.inv_m, tmag, 0.f);
+            if (lambda_t > lambda_n * avgMuS) {
+                applyPositional(x1, x2, q1, q2, fr1, fr2, m1.inv_m, m2.inv_m, t, lambda_t);
+            }
+        }
+    }
+    cdata[19] = lambda_n;
+
+    storeV3(S, BF_PX, b1, w, x1); storeV3(S, BF_PX, b2, w, x2);
+    storeQ(S, BF_QW, b1, w, q1); storeQ(S, BF_QW, b2, w, q2);
+}
+
+__device__ inline void handleFixedJoint(const DeviceState &S, int w, int k, int b1, int b2)
+{
+    MassData m1 = massOf(META(S, b1, w)), m2 = massOf(META(S, b2, w));
+    Vec3 x1 = loadPos(S, b1, w), x2 = loadPos(S, b2, w);
+    Quat q1 = loadRot(S, b1, w), q2 = loadRot(S, b2, w);
+    Quat a1 = {JF(S, JF_A1W, k, w), JF(S, JF_A1X, k, w), JF(S, JF_A1Y, k, w), JF(S, JF_A1Z, k, w)};
+    Quat a2 = {JF(S, JF_A2W, k, w), JF(S, JF_A2X, k, w), JF(S, JF_A2Y, k, w), JF(S, JF_A2Z, k, w)};
+    Vec3 jr1 = {JF(S, JF_R1X, k, w), JF(S, JF_R1Y, k, w), JF(S, JF_R1Z, k, w)};
+    Vec3 jr2 = {JF(S, JF_R2X, k, w), JF(S, JF_R2Y, k, w), JF(S, JF_R2Z, k, w)};
+    float sep = JF(S, JF_SEP, k, w);
+
+    // applyJointOrientationConstraint
+    {
+        Quat o1 = qnormalize(q1 * a1), o2 = qnormalize(q2 * a2);
+        Quat diff = o1 * qinv(o2);
+        Vec3 dq = 2.f * v3(diff.x, diff.y, diff.z);
+        float mag = length(dq);
+        if (mag > 0) {
+            dq = dq / mag;
+            Vec3 l1 = rotate(qinv(q1), dq), l2 = rotate(qinv(q2), dq);
+            Vec3 ra1 = mulDiag(m1.inv_I, l1), ra2 = mulDiag(m2.inv_I, l2);
+            float w1 = dot(l1, ra1), w2 = dot(l2, ra2);
+            float dl = -mag / (w1 + w2 + 0.f);
+            float half = 0.5f * dl;
+            Quat u1 = fromAngularVec(rotate(q1, half * ra1));
+            Quat u2 = fromAngularVec(rotate(q2, half * ra2));
+            q1 = qnormalize(q1 + u1 * q1);
+            q2 = qnormalize(q2 - u2 * q2);
+        }
+    }
+
+    Vec3 r1w = rotate(q1, jr1) + x1, r2w = rotate(q2, jr2) + x2;
+    Vec3 dr = r2w - r1w;
+    Quat axes = qnormalize(q1 * a1);
+    Vec3 ax = rotate(axes, v3(0, 1, 0));
+    Vec3 bx = rotate(axes, v3(1, 0, 0));
+    Vec3 cx = cross(ax, bx);
+    Vec3 corr = {0.f, 0.f, 0.f};
+    corr -= (dot(dr, ax) - sep) * ax;
+    corr -= dot(dr, bx) * bx;
+    corr -= dot(dr, cx) * cx;
+
+    float cmag = length(corr);
+    if (cmag > 0.f) {
+        corr = corr / cmag;
+        applyPositionalFull(x1, x2, q1, q2, jr1, jr2, m1, m2, corr, cmag, 0.f);
+    }
+    storeV3(S, BF_PX, b1, w, x1); storeV3(S, BF_PX, b2, w, x2);
+    storeQ(S, BF_QW, b1, w, q1); storeQ(S, BF_QW, b2, w, q2);
+}
+
+// solvePositions: one thread per world
+__global__ void k_solve_positions(DeviceState S)
+{
+    int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= S.p.numWorlds) return;
+    const int nc = WI(S, WF_NUM_CAND, w);
+    for (int c = 0; c < nc; c++) {
+        uint32_t meta = S.cmeta[size_t(w) * kMaxCand + c];
+        if ((meta >> 16) == 0) continue;
+        handleContact(S, w, meta, S.contact + (size_t(w) * kMaxCand + c) * kContactWords);
+    }
+
+    // joints in creation order
+    const int na = WI(S, WF_NUM_AGENTS, w);
+    const int nDyn = WI(S, WF_NUM_DYN, w);
+    int lastSeq = -1;
+    for (int it = 0; it < na; it++) {
+        int best = -1, bestSeq = 0x7FFFFFFF;
+        for (int k = 0; k < na; k++) {
+            uint32_t jm = JMETA(S, k, w);
+            if (jm == 0xFFFFFFFFu) continue;
+            int seq = int(jm >> 16);
+            if (seq > lastSeq && seq < bestSeq) { bestSeq = seq; best = k; }
+        }
+        if (best < 0) break;
+        lastSeq = bestSeq;
+        handleFixedJoint(S, w, best, nDyn + best, int(JMETA(S, best, w) & 0xFF));
+    }
+}
+
+// setVelocities: one thread per (slot, world)
+__global__ void k_set_velocities(DeviceState S)
+{
+    const int N = S.p.numWorlds;
+    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)kMaxBodies * N) return;
+    int s = int(idx / N), w = int(idx % N);
+    if (s >= WI(S, WF_NUM_BODIES, w)) return;
+
+    const float h = substepH();
+    Vec3 x = loadPos(S, s, w), xp = loadV3(S, BF_PREV_PX, s, w);
+    Quat q = loadRot(S, s, w), qp = loadQ(S, BF_PREV_QW, s, w);
+    Quat dq;
+    if (q.w != qp.w || q.x != qp.x || q.y != qp.y || q.z != qp.z) dq = q * qinv(qp);
+    else dq = {1.f, 0.f, 0.f, 0.f};
+    Vec3 newOmega = (2.f / h) * v3(dq.x, dq.y, dq.z);
+    storeV3(S, BF_VX, s, w, (x - xp) / h);
+    storeV3(S, BF_WX, s, w, dq.w > 0.f ? newOmega : -newOmega);
+}
+
+__device__ __forceinline__ Vec3 relVel(Vec3 v1, Vec3 v2, Vec3 o1, Vec3 o2, Vec3 d1, Vec3 d2)
+{
+    return (v1 + cross(o1, d1)) - (v2 + cross(o2, d2));
+}
+
+__device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_t meta, const float *cdata)
+{
+    const int b1 = meta & 0xFF, b2 = (meta >> 8) & 0xFF;
+    ContactView c = loadContact(cdata, meta);
+    const float lambdaN = cdata[19];
+    MassData m1 = massOf(META(S, b1, w)), m2 = massOf(META(S, b2, w));
+    const float h = substepH();
+    const float gMag = sqrtf(0.f * 0.f + 0.f * 0.f + 9.8f * 9.8f);
+    const float restThreshold = 2.f * gMag * h;
+
+    Vec3 v1 = loadV3(S, BF_VX, b1, w), o1 = loadV3(S, BF_WX, b1, w);
+    Vec3 v2 = loadV3(S, BF_VX, b2, w), o2 = loadV3(S, BF_WX, b2, w);
+    Quat q1 = loadRot(S, b1, w), q2 = loadRot(S, b2, w);
+    Vec3 px1 = loadV3(S, BF_PRE_PX, b1, w), px2 = loadV3(S, BF_PRE_PX, b2, w);
+    Quat pq1 = loadQ(S, BF_PRE_QW, b1, w), pq2 = loadQ(S, BF_PRE_QW, b2, w);
+    float muD = 0.5f * (m1.muD + m2.muD);
+    Vec3 n = c.normal;
+
+    {
+        Vec3 avg; float pen;
+        if (avgContact(c, &avg, &pen)) return;
+        Vec3 r1, r2;
+        localContacts(px1, pq1, px2, pq2, avg, pen, n, &r1, &r2);
+        Vec3 r1pre = rotate(pq1, r1), r2pre = rotate(pq2, r2);
+        Vec3 vbar = relVel(loadV3(S, BF_PRE_VX, b1, w), loadV3(S, BF_PRE_VX, b2, w),
+                           loadV3(S, BF_PRE_WX, b1, w), loadV3(S, BF_PRE_WX, b2, w), r1pre, r2pre);
+        float vnBar = dot(n, vbar);
+        Vec3 r1w = rotate(q1, r1), r2w = rotate(q2, r2);
+        Vec3 ta1 = cross(r1, rotate(qinv(q1), n)), ta2 = cross(r2, rotate(qinv(q2), n));
+
+        // applyRestitutionVelocityUpdate
+        Vec3 v = relVel(v1, v2, o1, o2, r1w, r2w);
+        float vn = dot(n, v);
+        float e = 0.3f;
+        if (fabsf(vnBar) <= restThreshold) e = 0.f;
+        float mag = fminf(-e * vnBar, 0) - vn;
+        Vec3 ra1 = mulDiag(m1.inv_I, ta1), ra2 = mulDiag(m2.inv_I, ta2);
+        float w1 = m1.inv_m + dot(ta1, ra1), w2 = m2.inv_m + dot(ta2, ra2);
+        float invScale = 1.f / (w1 + w2);
+        float imp = mag * invScale;
+        if (imp != 0.f) {
+            v1 += n * imp * m1.inv_m;
+            v2 -= n * imp * m2.inv_m;
+            o1 += rotate(q1, imp * ra1);
+            o2 -= rotate(q2, imp * ra2);
+        }
+    }
+
+    float penSum = 0.f;
+    for (int i = 0; i < c.n; i++) penSum += c.depth[i];
+
+    for (int i = 0; i < c.n; i++) {
+        Vec3 r1, r2;
+        localContacts(px1, pq1, px2, pq2, c.pts[i], c.depth[i], n, &r1, &r2);
+        Vec3 r1w = rotate(q1, r1), r2w = rotate(q2, r2);
+        float lambda = lambdaN * (c.depth[i] / penSum);
+
+        // applyFrictionVelocityUpdate
+        Vec3 v = relVel(v1, v2, o1, o2, r1w, r2w);
+        float vn = dot(n, v);
+        Vec3 vt = v - n * vn;
+        float vtLen = length(vt);
+        if (vtLen == 0.f) continue;
+        Vec3 dw = vt / vtLen;
+        Vec3 d1 = rotate(qinv(q1), dw), d2 = rotate(qinv(q2), dw);
+        Vec3 fa1 = cross(r1, d1), fa2 = cross(r2, d2);
+        Vec3 fr1 = mulDiag(m1.inv_I, fa1), fr2 = mulDiag(m2.inv_I, fa2);
+        float w1 = m1.inv_m + dot(fa1, fr1), w2 = m2.inv_m + dot(fa2, fr2);
+        float invScale = 1.f / (w1 + w2);
+        float fmag = muD * fabsf(lambda) * invScale / h;
+        float corrected = -fminf(fmag, vtLen);
+        float imp = corrected * invScale;
+        if (imp == 0.f) continue;
+        v1 += dw * imp * m1.inv_m;
+        v2 -= dw * imp * m2.inv_m;
+        o1 += rotate(q1, imp * fr1);
+        o2 -= rotate(q2, imp * fr2);
+    }
+
+    storeV3(S, BF_VX, b1, w, v1); storeV3(S, BF_WX, b1, w, o1);
+    storeV3(S, BF_VX, b2, w, v2); storeV3(S, BF_WX, b2, w, o2);
+}
+
+// solveVelocities: one thread per world
+__global__ void k_solve_velocities(DeviceState S)
+{
+    int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= S.p.numWorlds) return;
+    const int nc = WI(S, WF_NUM_CAND, w);
+    for (int c = 0; c < nc; c++) {
+        uint32_t meta = S.cmeta[size_t(w) * kMaxCand + c];
+        if ((meta >> 16) == 0) continue;
+        solveContactVelocity(S, w, meta, S.contact + (size_t(w) * kMaxCand + c) * kContactWords);
+    }
+}
+
+}  // namespace hs
