@@ -266,6 +266,19 @@ struct Launcher {
     const DeviceState &S;
     cudaStream_t st;
     int count = 0;
+    std::vector<cudaEvent_t> *events = nullptr;     // profiling mode: one event after each launch
+    std::vector<const char *> *names = nullptr;
+    void mark(const char *name)
+    {
+        count++;
+        if (events) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            cudaEventRecord(e, st);
+            events->push_back(e);
+            names->push_back(name);
+        }
+    }
     int N() const { return S.p.numWorlds; }
     // thread per world
     dim3 gWorld(int block = 128) const { return dim3((N() + block - 1) / block); }
@@ -282,41 +295,41 @@ struct Launcher {
 // setupBVHTasks (broadphase.cpp:995-1017): update leaves, rebuild if forced, refit
 void launchBroadphaseSetup(Launcher &L, bool mayRebuild)
 {
-    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
-    if (mayRebuild) { k_bvh_rebuild<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++; }
-    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_leaf_update");
+    if (mayRebuild) { k_bvh_rebuild<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_bvh_rebuild"); }
+    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_refit");
 }
 
 // observationsTasks (src/sim.cpp:1232-1293)
 void launchObservations(Launcher &L, float cosThr)
 {
-    k_observations<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.count++;
-    k_visibility<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S, cosThr); L.count++;
-    k_lidar<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.count++;
-    k_debug_positions<<<L.gWorld(), 128, 0, L.st>>>(L.S); L.count++;
+    k_observations<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.mark("k_observations");
+    k_visibility<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S, cosThr); L.mark("k_visibility");
+    k_lidar<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.mark("k_lidar");
+    k_debug_positions<<<L.gWorld(), 128, 0, L.st>>>(L.S); L.mark("k_debug_positions");
 }
 
 // Step task graph (src/sim.cpp:1307-1313), node order of SURVEY.md §3.3
 void launchStep(Launcher &L, float cosThr)
 {
-    k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.count++;
+    k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.mark("k_move");
     launchBroadphaseSetup(L, true);
-    k_action<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
-    k_broadphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.count++;
+    k_action<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_action");
+    k_broadphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.mark("k_broadphase");
     for (int i = 0; i < kSubsteps; i++) {
-        k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
-        k_narrowphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.count++;
-        k_solve_positions<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
-        k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
-        k_solve_velocities<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
+        k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep");
+        k_narrowphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.mark("k_narrowphase");
+        k_solve_positions<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_solve_positions");
+        k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_set_velocities");
+        k_solve_velocities<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_solve_velocities");
     }
-    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
-    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.count++;
+    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_leaf_update");
+    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_refit");
     if (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) {
-        k_zero_agent_vel<<<dim3((L.N() * kMaxAgents + 127) / 128), 128, 0, L.st>>>(L.S); L.count++;
+        k_zero_agent_vel<<<dim3((L.N() * kMaxAgents + 127) / 128), 128, 0, L.st>>>(L.S); L.mark("k_zero_agent_vel");
     }
-    k_rewards<<<L.gWorld(64), 64, 0, L.st>>>(L.S, cosThr); L.count++;
-    k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.count++;
+    k_rewards<<<L.gWorld(64), 64, 0, L.st>>>(L.S, cosThr); L.mark("k_rewards");
+    k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_reset");
     launchBroadphaseSetup(L, true);
     launchObservations(L, cosThr);
 }
@@ -437,4 +450,43 @@ extern "C" int hs_step_host(hs_sim *sim, void *stream, const int32_t *actions_ho
     if (done_host)
         HS_CUDA(cudaMemcpyAsync(done_host, sim->S.exDone, R * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     return 0;
+}
+
+// Instrumented step: same launch sequence without the graph, one CUDA event
+// after every kernel on `stream`; returns per-launch durations.  Used by
+// bench.py for the roofline object; not on the product path.
+static thread_local std::vector<const char *> g_profNames;
+
+extern "C" int hs_step_profiled(hs_sim *sim, void *stream, float *ms_out, int cap, int *n_out)
+{
+    if (!sim || !sim->inited) { g_err = "hs_step_profiled: hs_init has not run"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    cudaStream_t st = (cudaStream_t)stream;
+    std::vector<cudaEvent_t> ev;
+    g_profNames.clear();
+    cudaEvent_t start;
+    HS_CUDA(cudaEventCreate(&start));
+    HS_CUDA(cudaEventRecord(start, st));
+    Launcher L{sim->S, st};
+    L.events = &ev;
+    L.names = &g_profNames;
+    launchStep(L, sim->cosThreshold);
+    HS_CUDA(cudaStreamSynchronize(st));
+    cudaEvent_t prev = start;
+    int n = 0;
+    for (size_t i = 0; i < ev.size(); i++) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, prev, ev[i]);
+        if (n < cap) ms_out[n++] = ms;
+        prev = ev[i];
+    }
+    cudaEventDestroy(start);
+    for (cudaEvent_t e : ev) cudaEventDestroy(e);
+    *n_out = n;
+    return 0;
+}
+
+extern "C" const char *hs_profiled_kernel_name(int i)
+{
+    return (i >= 0 && i < (int)g_profNames.size()) ? g_profNames[i] : "";
 }

@@ -10,7 +10,7 @@ def ref_bodies(rw):
     return rw["bodies"][: rw["num_bodies"]]
 
 
-def compare_world_static(rw, hw, exact=True, tol=0.0):
+def compare_world_static(rw, hw, exact=True, tol=0.0, check_scores=True):
     """Compare body tables + bookkeeping. Returns list of mismatch strings."""
     errs = []
     nb = int(rw["num_bodies"])
@@ -40,7 +40,8 @@ def compare_world_static(rw, hw, exact=True, tol=0.0):
             errs.append(f"{f}: ref {int(rw[f])} hs {int(hw[g])}")
     if not np.array_equal(rw["rng_key"], hw["rng_key"]):
         errs.append("episode rng key mismatch")
-    if not np.array_equal(rw["running_scores"], hw["running_scores"]):
+    # EpisodeStats is uninitialised memory in the reference until the first step of an episode
+    if check_scores and not np.array_equal(rw["running_scores"], hw["running_scores"]):
         errs.append("running scores mismatch")
     if float(rw["hider_team_reward"]) != float(hw["hider_team_reward"]):
         errs.append("hider_team_reward mismatch")
@@ -84,3 +85,47 @@ def compare_bvh(rw, hw, exact=True, tol=0.0):
     elif np.abs(la_r.astype(np.float64) - la_h).max() > tol:
         errs.append("leaf aabbs differ beyond tol")
     return errs
+
+
+# (binding getter, reference key, float-exactness class)
+EXPORTS = [("seed", "seed", "int"), ("self_type", "self_type", "int"), ("self_mask", "self_mask", "mask"),
+           ("action", "action", "int"), ("prep_counter", "prep_counter", "int"),
+           ("reward", "reward", "exactf"), ("done", "done", "int"),
+           ("lidar", "lidar", "float"), ("self_data", "self_obs", "float"),
+           ("agent_data", "agent_obs", "float"), ("box_data", "box_obs", "float"),
+           ("ramp_data", "ramp_obs", "float"),
+           ("visible_agents_mask", "agent_vis", "exactf"), ("visible_boxes_mask", "box_vis", "exactf"),
+           ("visible_ramps_mask", "ramp_vis", "exactf"),
+           ("episode_result", "episode_result", "world"), ("global_positions", "global_pos", "globalpos")]
+
+
+def compare_exports(sim, rt, min_agents, tol, skip=()):
+    """Compare every exported tensor.  Rows of inactive agent interfaces hold
+    uninitialised memory in the reference and are skipped.
+    Returns (errors, max float difference)."""
+    errs, maxd = [], 0.0
+    active = rt["self_mask"].reshape(-1) == 1.0
+    for name, key, kind in EXPORTS:
+        if name in skip:
+            continue
+        mine = getattr(sim, name + "_tensor")().to_torch().cpu().numpy()
+        theirs = np.asarray(rt[key]).reshape(mine.shape)
+        if kind == "mask":
+            if not np.array_equal(mine, theirs):
+                errs.append(name)
+            continue
+        if kind == "globalpos":
+            k = 11 + min_agents
+            mine, theirs = mine[:, :k], theirs[:, :k]
+        elif kind != "world":
+            mine, theirs = mine[active], theirs[active]
+        if kind == "int":
+            if not np.array_equal(mine, theirs):
+                errs.append(name)
+        else:
+            d = float(np.abs(mine.astype(np.float64) - theirs).max()) if mine.size else 0.0
+            maxd = max(maxd, d)
+            lim = 0.0 if kind == "exactf" else tol
+            if not (d <= lim):
+                errs.append(f"{name}: max abs diff {d}")
+    return errs, maxd

@@ -1,0 +1,91 @@
+"""Step transitions vs the reference CPU backend (oracle/_ref) on the same seed
+and the same action tape.
+
+Bars (BASELINE.json north_star): grab/lock state and lidar hit structure exact;
+positions / velocities / lidar depths within a float tolerance.  Both sides
+evaluate IEEE fp32 in the same operation order without FMA contraction, so the
+observed difference is normally zero; the tolerance below is the stated bar,
+and the test prints the measured maximum.
+"""
+import numpy as np
+import pytest
+
+import refsim
+from parity import compare_world_static, compare_bvh, compare_exports
+
+pytestmark = pytest.mark.gpu
+
+POS_TOL = 1e-4      # abs, positions / quaternions / velocities / lidar depth, per step
+
+
+def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, check_every=1):
+    import gpu_hideseek as gh
+    ref = refsim.RefSim(N, sim_flags=flags, seed=seed, min_hiders=hs[0], max_hiders=hs[1],
+                        min_seekers=sk[0], max_seekers=sk[1], num_threads=1)
+    ref.init()
+    sim = gh.HideAndSeekSimulator(num_worlds=N, sim_flags=flags, rand_seed=seed, min_hiders=hs[0],
+                                  max_hiders=hs[1], min_seekers=sk[0], max_seekers=sk[1])
+    sim.init()
+    rt = ref.tensors()
+    act = sim.action_tensor().to_torch()
+    import torch
+    rng = np.random.RandomState(1234 + seed)
+    A = hs[1] + sk[1]
+    zero_vel = bool(flags & 8)
+    maxdiff = 0.0
+    for step in range(steps):
+        a = np.zeros((N * A, 5), dtype=np.int32)
+        if zero_vel:
+            a[:, 0:3] = rng.randint(0, 5, size=(N * A, 3))
+        else:
+            a[:, 0:3] = rng.randint(0, 11, size=(N * A, 3))
+        if use_grab_lock:
+            a[:, 3] = rng.rand(N * A) < 0.3
+            a[:, 4] = rng.rand(N * A) < 0.15
+        rt["action"][:] = a
+        act.copy_(torch.from_numpy(a).to(act.device))
+        ref.step()
+        sim.step()
+        if step % check_every and step != steps - 1:
+            continue
+        for w in range(N):
+            rw, hw = ref.dump_world(w), sim.dump_world(w)
+            errs = compare_world_static(rw, hw, exact=False, tol=POS_TOL)
+            errs += compare_bvh(rw, hw, exact=False, tol=POS_TOL)
+            # joints: same set, same partners
+            rj = sorted((int(j["e1"]), int(j["e2"])) for j in rw["joints"][: rw["num_joints"]])
+            eid2slot = {int(b["entity_id"]): i for i, b in enumerate(rw["bodies"][: rw["num_bodies"]])}
+            rj = sorted((eid2slot[a_], eid2slot[b_]) for a_, b_ in rj)
+            nd = int(hw["num_dyn"])
+            hj = sorted((nd + k, int(j["other_slot"])) for k, j in enumerate(hw["joints"]) if j["active"])
+            if rj != hj:
+                errs.append(f"joints ref {rj} hs {hj}")
+            assert not errs, (step, w, errs[:5])
+            nb = int(rw["num_bodies"])
+            for f in ("pos", "rot", "vel"):
+                maxdiff = max(maxdiff, float(np.abs(rw["bodies"][f][:nb] - hw["bodies"][f][:nb]).max()))
+        errs, d = compare_exports(sim, rt, hs[0] + sk[0], tol=5e-4)
+        assert not errs, (step, errs)
+        maxdiff = max(maxdiff, d)
+    print(f"max abs difference over {steps} steps: {maxdiff:g}")
+    assert sim.overflow_count() == 0
+    return maxdiff
+
+
+def test_random_moves_100_steps():
+    _run_pair(32, seed=0, flags=0, steps=100, check_every=5)
+
+
+def test_grab_lock_state_machine():
+    _run_pair(32, seed=5, flags=0, steps=130, use_grab_lock=True, check_every=10)
+
+
+def test_zero_vel_fixed_world_flip_teams():
+    # jax_train.py flags: RandomFlipTeams | UseFixedWorld | ZeroAgentVelocity, 3+3 agents
+    _run_pair(16, seed=5, flags=4 | 1 | 8, steps=110, hs=(3, 3), sk=(3, 3), use_grab_lock=True,
+              check_every=10)
+
+
+def test_episode_rollover_resets():
+    # crosses step 239 -> automatic reset -> second episode level must be bit-exact again
+    _run_pair(8, seed=3, flags=0, steps=245, hs=(1, 3), sk=(1, 3), check_every=40)
