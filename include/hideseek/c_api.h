@@ -88,6 +88,13 @@ int hs_world_dump_bytes(void);
 int hs_last_step_launches(hs_sim *sim);
 int hs_overflow_count(hs_sim *sim, uint32_t *out);
 
+/* Measurement only (bench.py roofline): one step launched kernel by kernel with a
+ * CUDA event after each launch on `stream`; per-launch milliseconds in ms_out. */
+int hs_step_profiled(hs_sim *sim, void *stream, float *ms_out, int cap, int *n_out);
+const char *hs_profiled_kernel_name(int i);
+/* totals over the shard: live bodies, active agents, candidates, contacts */
+int hs_world_stats(hs_sim *sim, int64_t *out4);
+
 const char *hs_last_error(void);
 
 #ifdef __cplusplus

@@ -490,3 +490,34 @@ extern "C" const char *hs_profiled_kernel_name(int i)
 {
     return (i >= 0 && i < (int)g_profNames.size()) ? g_profNames[i] : "";
 }
+
+// Measurement only: totals over the shard of live bodies, agents, broadphase
+// candidates and contacts of the most recent substep (bench.py uses the means to
+// scale the algorithmic-bytes figures of DESIGN.md).
+extern "C" int hs_world_stats(hs_sim *sim, int64_t *out4)
+{
+    if (!sim || !out4) { g_err = "hs_world_stats: null argument"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    HS_CUDA(cudaDeviceSynchronize());
+    const size_t N = sim->cfg.num_worlds;
+    std::vector<int32_t> row(N);
+    std::vector<int32_t> ncand(N);
+    auto sumRow = [&](int f, std::vector<int32_t> &dst, int64_t *acc) -> int {
+        HS_CUDA(cudaMemcpy(dst.data(), sim->S.wi + size_t(f) * N, N * 4, cudaMemcpyDeviceToHost));
+        int64_t s = 0;
+        for (int32_t v : dst) s += v;
+        *acc = s;
+        return 0;
+    };
+    HS_TRY(sumRow(WF_NUM_BODIES, row, &out4[0]));
+    HS_TRY(sumRow(WF_NUM_AGENTS, row, &out4[1]));
+    HS_TRY(sumRow(WF_NUM_CAND, ncand, &out4[2]));
+    std::vector<uint32_t> cm(N * kMaxCand);
+    HS_CUDA(cudaMemcpy(cm.data(), sim->S.cmeta, cm.size() * 4, cudaMemcpyDeviceToHost));
+    int64_t k = 0;
+    for (size_t w = 0; w < N; w++)
+        for (int c = 0; c < ncand[w]; c++)
+            if (cm[w * kMaxCand + c] >> 16) k++;
+    out4[3] = k;
+    return 0;
+}

@@ -34,6 +34,7 @@ C_API_SYMBOLS = [
     "hs_create", "hs_destroy", "hs_init", "hs_step", "hs_sync", "hs_export",
     "hs_trigger_reset", "hs_set_action", "hs_step_host", "hs_dump_world",
     "hs_world_dump_bytes", "hs_last_step_launches", "hs_overflow_count", "hs_last_error",
+    "hs_step_profiled", "hs_profiled_kernel_name", "hs_world_stats",
 ]
 
 
@@ -70,6 +71,9 @@ def load_library():
     l.hs_last_step_launches.argtypes = [C.c_void_p]
     l.hs_overflow_count.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
     l.hs_last_error.restype = C.c_char_p
+    l.hs_step_profiled.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_int)]
+    l.hs_profiled_kernel_name.argtypes = [C.c_int]
+    l.hs_profiled_kernel_name.restype = C.c_char_p
     _lib = l
     return l
 
@@ -195,6 +199,21 @@ class HideAndSeekSimulator:
         assert self._lib.hs_world_dump_bytes() == world_dt.itemsize
         _check(self._lib.hs_dump_world(self._h, world, out.ctypes.data, world_dt.itemsize))
         return out[0]
+
+    def step_profiled(self, stream=0):
+        """One un-graphed step with a CUDA event after every kernel; returns [(name, ms)]."""
+        ms = (C.c_float * 128)()
+        n = C.c_int()
+        _check(self._lib.hs_step_profiled(self._h, C.c_void_p(stream), ms, 128, C.byref(n)))
+        return [(self._lib.hs_profiled_kernel_name(i).decode(), ms[i]) for i in range(n.value)]
+
+    def world_stats(self):
+        """Mean live bodies, agents, candidates, contacts per world (measurement only)."""
+        out = (C.c_int64 * 4)()
+        self._lib.hs_world_stats.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        _check(self._lib.hs_world_stats(self._h, out))
+        n = float(self.num_worlds)
+        return dict(bodies=out[0] / n, agents=out[1] / n, candidates=out[2] / n, contacts=out[3] / n)
 
     def last_step_launches(self):
         return self._lib.hs_last_step_launches(self._h)
