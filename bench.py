@@ -120,6 +120,12 @@ def kernel_alg_bytes(name, A, E, C, K):
     return float(table.get(name, 0))
 
 
+def aggregate_value(n_per_rank, world, steps, ms_total):
+    """Whole-job env-steps/s: every rank steps n_per_rank worlds (weak scaling, no data-path
+    collective); ms_total is the max over ranks of the device-timed region."""
+    return n_per_rank * world * steps / (ms_total / 1000.0)
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -223,7 +229,7 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
-    value = N * world * args.steps / (ms_total / 1000.0)
+    value = aggregate_value(N, world, args.steps, ms_total)
 
     # ---- end to end through the C ABI with HOST buffers (pinned), copies timed ------------
     R = N * A

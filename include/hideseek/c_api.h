@@ -80,6 +80,18 @@ int hs_set_action(hs_sim *sim, int agent_row, int x, int y, int r, int g, int l)
 int hs_step_host(hs_sim *sim, void *stream, const int32_t *actions_host,
                  float *reward_host, int32_t *done_host);
 
+/* Manager::saveCheckpoint / loadCheckpoint / loadCheckpoints (src/mgr.cpp:905-985) and the
+ * SaveCheckpoints / LoadCheckpoints task graphs (src/sim.cpp:956-1137, 1315-1344).
+ * hs_save_checkpoint / hs_load_checkpoint set CheckpointControl.trigger of one world and run the
+ * corresponding graph synchronously; the *_checkpoints variants run the graph over every
+ * world whose trigger is already set in the exported CheckpointControl tensor (the JAX path,
+ * src/mgr.cpp:400-437), asynchronously on `stream`.  The Checkpoint tensor keeps the
+ * reference's byte layout (src/sim.hpp:283-313). */
+int hs_save_checkpoint(hs_sim *sim, int world);
+int hs_load_checkpoint(hs_sim *sim, int world);
+int hs_save_checkpoints(hs_sim *sim, void *stream);
+int hs_load_checkpoints(hs_sim *sim, void *stream);
+
 /* Diagnostics / parity: flat per-world internal state (layout in
  * hideseek/debug_dump.h), number of kernels launched by the last hs_step,
  * capacity-overflow counter. */

@@ -433,8 +433,59 @@ __device__ inline void generateTrainingWorld(const DeviceState &S, int w, Rng &e
     WI(S, WF_NUM_RAMPS, w) = kMaxRamps;
 }
 
-// resetSystem (src/sim.cpp:172-200).  forceLevel >= 0 overrides the exported
-// reset flag (used by init, where the reference constructor sets resetLevel = 1).
+// resetEnvironment + generateEnvironment for one world.  `ckpt == nullptr`: the episode
+// reset of resetSystem (new episode key, agent counts drawn from the episode RNG).
+// `ckpt != nullptr`: the regeneration half of loadCheckpointSystem (src/sim.cpp:966-985):
+// the episode key comes from the checkpoint, the episode counter is not advanced, the two
+// agent-count draws are burned and the saved counts are used instead.
+struct CkptRegen { RandKey key; int numHiders, numSeekers; };
+
+__device__ inline void regenerateWorld(const DeviceState &S, int w, const CkptRegen *ckpt)
+{
+    IdPool ids(S, w);
+    WI(S, WF_EPISODE_STEP, w) = 0;
+    uint32_t *blob = BVH(S, w);
+    blob[2] = 1;        // PhysicsSystem::reset -> rebuildOnUpdate + clearLeaves
+    blob[1] = 0;
+    teardownWorld(S, w, ids);
+
+    RandKey epKey;
+    if (ckpt) {
+        epKey = ckpt->key;
+    } else {
+        // initEpisodeRNG (src/sim.cpp:105-114)
+        uint32_t ep = (uint32_t)WI(S, WF_WORLD_EPISODE, w);
+        WI(S, WF_WORLD_EPISODE, w) = int32_t(ep + 1);
+        epKey = RandKey{ep, uint32_t(S.p.worldBase + w)};
+    }
+    WI(S, WF_EP_KEY_A, w) = (int32_t)epKey.a;
+    WI(S, WF_EP_KEY_B, w) = (int32_t)epKey.b;
+    Rng rng{splitKey(RandKey{S.p.initKeyA, S.p.initKeyB}, epKey.a, epKey.b), 0};
+
+    int numHiders = rng.sampleI32(S.p.minHiders, S.p.maxHiders + 1);
+    int numSeekers = rng.sampleI32(S.p.minSeekers, S.p.maxSeekers + 1);
+    if (ckpt) { numHiders = ckpt->numHiders; numSeekers = ckpt->numSeekers; }
+    RandKey lvlKey = rng.advance();        // levelGenRandKey always draws
+    if (S.p.simFlags & FLAG_FIXED_WORLD) lvlKey = {0, 0};
+
+    generateTrainingWorld(S, w, rng, lvlKey, numHiders, numSeekers, ids);
+
+    // generateEnvironment tail (level_gen.cpp:326-333): park unused interfaces
+    int nAgents = WI(S, WF_NUM_AGENTS, w);
+    for (int k = nAgents; k < S.p.agentsPerWorld; k++) {
+        WB(S, WB_IFACE_SLOT + k, w) = 0xFF;
+        S.exSelfMask[size_t(w) * S.p.agentsPerWorld + k] = 0.f;
+    }
+
+    blob[1] = (uint32_t)WI(S, WF_NUM_BODIES, w);
+    WI(S, WF_RNG_A, w) = (int32_t)rng.k.a;
+    WI(S, WF_RNG_B, w) = (int32_t)rng.k.b;
+    WI(S, WF_RNG_COUNT, w) = (int32_t)rng.count;
+    WI(S, WF_DID_RESET, w) = 1;
+    ids.commit();
+}
+
+// resetSystem (src/sim.cpp:172-200), one thread per world.
 __global__ void k_reset(DeviceState S)
 {
     int w = blockIdx.x * blockDim.x + threadIdx.x;
@@ -445,42 +496,8 @@ __global__ void k_reset(DeviceState S)
     if ((S.p.simFlags & FLAG_IGNORE_EPISODE_LEN) == 0 && step == kEpisodeLen - 1) level = 1;
 
     if (level != 0) {
-        IdPool ids(S, w);
-        WI(S, WF_EPISODE_STEP, w) = 0;
-        uint32_t *blob = BVH(S, w);
-        blob[2] = 1;        // PhysicsSystem::reset -> rebuildOnUpdate + clearLeaves
-        blob[1] = 0;
-        teardownWorld(S, w, ids);
         S.exReset[w] = 0;
-
-        // initEpisodeRNG (src/sim.cpp:105-114)
-        uint32_t ep = (uint32_t)WI(S, WF_WORLD_EPISODE, w);
-        WI(S, WF_WORLD_EPISODE, w) = int32_t(ep + 1);
-        RandKey epKey{ep, uint32_t(S.p.worldBase + w)};
-        WI(S, WF_EP_KEY_A, w) = (int32_t)epKey.a;
-        WI(S, WF_EP_KEY_B, w) = (int32_t)epKey.b;
-        Rng rng{splitKey(RandKey{S.p.initKeyA, S.p.initKeyB}, epKey.a, epKey.b), 0};
-
-        int numHiders = rng.sampleI32(S.p.minHiders, S.p.maxHiders + 1);
-        int numSeekers = rng.sampleI32(S.p.minSeekers, S.p.maxSeekers + 1);
-        RandKey lvlKey = rng.advance();        // levelGenRandKey always draws
-        if (S.p.simFlags & FLAG_FIXED_WORLD) lvlKey = {0, 0};
-
-        generateTrainingWorld(S, w, rng, lvlKey, numHiders, numSeekers, ids);
-
-        // generateEnvironment tail (level_gen.cpp:326-333): park unused interfaces
-        int nAgents = WI(S, WF_NUM_AGENTS, w);
-        for (int k = nAgents; k < S.p.agentsPerWorld; k++) {
-            WB(S, WB_IFACE_SLOT + k, w) = 0xFF;
-            S.exSelfMask[size_t(w) * S.p.agentsPerWorld + k] = 0.f;
-        }
-
-        blob[1] = (uint32_t)WI(S, WF_NUM_BODIES, w);
-        WI(S, WF_RNG_A, w) = (int32_t)rng.k.a;
-        WI(S, WF_RNG_B, w) = (int32_t)rng.k.b;
-        WI(S, WF_RNG_COUNT, w) = (int32_t)rng.count;
-        WI(S, WF_DID_RESET, w) = 1;
-        ids.commit();
+        regenerateWorld(S, w, nullptr);
     } else {
         WI(S, WF_EPISODE_STEP, w) = step + 1;
         WI(S, WF_DID_RESET, w) = 0;

@@ -23,6 +23,7 @@
 #include "hs_obs.cuh"
 #include "hs_narrowphase.cuh"
 #include "hs_solver.cuh"
+#include "hs_checkpoint.cuh"
 
 namespace hs {
 void buildAssetTable(AssetTable &T);
@@ -432,6 +433,56 @@ extern "C" int hs_step(hs_sim *sim, void *stream)
         sim->lastLaunches = L.count;
     }
     HS_CUDA(cudaGraphLaunch(sim->stepGraph, st));
+    return 0;
+}
+
+// ---- checkpoints (SaveCheckpoints / LoadCheckpoints task graphs, src/sim.cpp:1315-1332) ------
+extern "C" int hs_save_checkpoints(hs_sim *sim, void *stream)
+{
+    if (!sim || !sim->inited) { g_err = "hs_save_checkpoints: hs_init has not run"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    Launcher L{sim->S, (cudaStream_t)stream};
+    k_save_checkpoint<<<L.gWorld(), 128, 0, L.st>>>(L.S);
+    HS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int hs_load_checkpoints(hs_sim *sim, void *stream)
+{
+    if (!sim || !sim->inited) { g_err = "hs_load_checkpoints: hs_init has not run"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    Launcher L{sim->S, (cudaStream_t)stream};
+    k_load_checkpoint<<<L.gWorld(64), 64, 0, L.st>>>(L.S);
+    launchBroadphaseSetup(L, true);            // postGenTasks
+    launchObservations(L, sim->cosThreshold);  // observationsTasks
+    HS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int setCkptTrigger(hs_sim *sim, int world, const char *who)
+{
+    if (!sim || world < 0 || world >= sim->cfg.num_worlds) { g_err = std::string(who) + ": bad world"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    int32_t one = 1;
+    HS_CUDA(cudaMemcpy(sim->S.exCkptCtrl + world, &one, 4, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+// Manager::saveCheckpoint / loadCheckpoint (src/mgr.cpp:905-964): set one world's trigger,
+// run the graph, wait.
+extern "C" int hs_save_checkpoint(hs_sim *sim, int world)
+{
+    HS_TRY(setCkptTrigger(sim, world, "hs_save_checkpoint"));
+    HS_TRY(hs_save_checkpoints(sim, nullptr));
+    HS_CUDA(cudaStreamSynchronize(nullptr));
+    return 0;
+}
+
+extern "C" int hs_load_checkpoint(hs_sim *sim, int world)
+{
+    HS_TRY(setCkptTrigger(sim, world, "hs_load_checkpoint"));
+    HS_TRY(hs_load_checkpoints(sim, nullptr));
+    HS_CUDA(cudaStreamSynchronize(nullptr));
     return 0;
 }
 

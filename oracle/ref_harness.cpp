@@ -371,4 +371,62 @@ double hsref_bench(void *hp, int warmup, int steps, uint32_t action_seed)
     return std::chrono::duration<double>(t1 - t0).count();
 }
 
+
+// ---- known-answer entry points: the reference's own RNG / math routines, so that the
+// tests can replay the reference's unit-test vectors (M/tests/rand.cpp:131-140,
+// M/tests/math.cpp:23-47) against this build and against the CUDA library's host-compiled
+// headers. ---------------------------------------------------------------------------------
+void hsref_rand_split(uint32_t a, uint32_t b, uint32_t idx, uint32_t idx_upper, uint32_t *out)
+{
+    madrona::RandKey k = madrona::rand::split_i(madrona::RandKey{a, b}, idx, idx_upper);
+    out[0] = k.a; out[1] = k.b;
+}
+
+void hsref_rand_init_key(uint32_t seed, uint32_t *out)
+{
+    madrona::RandKey k = madrona::rand::initKey(seed);
+    out[0] = k.a; out[1] = k.b;
+}
+
+uint32_t hsref_rand_bits32(uint32_t a, uint32_t b) { return madrona::rand::bits32(madrona::RandKey{a, b}); }
+
+int32_t hsref_rand_sample_i32(uint32_t a, uint32_t b, int32_t lo, int32_t hi)
+{
+    return madrona::rand::sampleI32(madrona::RandKey{a, b}, lo, hi);
+}
+
+float hsref_rand_sample_uniform(uint32_t a, uint32_t b)
+{
+    return madrona::rand::sampleUniform(madrona::RandKey{a, b});
+}
+
+// RNG(seed) stream: n draws of sampleUniform (even slots) / sampleI32(lo,hi) (odd slots)
+void hsref_rng_stream(uint32_t seed, int n, int32_t lo, int32_t hi, float *uni, int32_t *ints)
+{
+    madrona::RNG rng(seed);
+    for (int i = 0; i < n; i++) {
+        uni[i] = rng.sampleUniform();
+        ints[i] = rng.sampleI32(lo, hi);
+    }
+}
+
+void hsref_quat_angle_axis(float angle, const float *axis, float *out)
+{
+    madrona::math::Quat q = madrona::math::Quat::angleAxis(angle, {axis[0], axis[1], axis[2]});
+    out[0] = q.w; out[1] = q.x; out[2] = q.y; out[3] = q.z;
+}
+
+void hsref_quat_mul(const float *a, const float *b, float *out)
+{
+    madrona::math::Quat q = madrona::math::Quat{a[0], a[1], a[2], a[3]} *
+                            madrona::math::Quat{b[0], b[1], b[2], b[3]};
+    out[0] = q.w; out[1] = q.x; out[2] = q.y; out[3] = q.z;
+}
+
+void hsref_quat_rotate(const float *q, const float *v, float *out)
+{
+    madrona::math::Vector3 r = madrona::math::Quat{q[0], q[1], q[2], q[3]}.rotateVec({v[0], v[1], v[2]});
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+
 }
