@@ -1,0 +1,305 @@
+// Fused ray stage: 30-ray lidar + visibility masks for every agent of a world in ONE kernel.
+//
+// Behavioural contract (unchanged from hs_obs.cuh / hs_trace.cuh):
+//   computeVisibilitySystem (CPU branch, incl. hiderTeamReward side effect)  src/sim.cpp:567-605, 663-709
+//   lidarSystem                                                             src/sim.cpp:712-759
+//   BVH::traceRay / traceRayIntoLeaf / ...                                  M/src/physics/broadphase.cpp:658-890
+//
+// Mapping (B200): one CTA per world.  The world's BVH tile (header + nodes + leaves, the
+// contiguous world-major blob of hs_state.cuh) and the hull/object table are staged in shared
+// memory once; every ray of the world — A*30 lidar rays plus the visibility rays that pass the
+// view-cone test, compacted into a shared queue — is then one lane's work item, so warps are
+// full regardless of how many targets an agent has.
+//
+// Traversal is warp-convergent: every lane walks its own ray through the 4-wide tree (all four
+// child slabs of a node are tested in straight-line code from float4 shared loads), but a lane
+// that reaches a leaf parks until a warp vote finds enough parked lanes, and the (expensive,
+// formerly 4x-inlined) ray-vs-hull test then runs once for all of them.  Per-lane visiting order
+// — pop LIFO, children 0..3, leaves tested at the moment they are met with the current t_max —
+// is exactly the reference's, so hit entities are identical even for exact ties.
+#pragma once
+
+#include "hs_trace.cuh"
+
+namespace hs {
+
+constexpr int kRayThreads = 160;
+constexpr int kMaxVisRays = kMaxAgents * (kMaxBoxes + kMaxRamps + kMaxAgents - 1);   // 96
+
+__constant__ float c_lidarDir[30][2];     // (cos, sin) of theta_i, hs_det_sincosf on the host
+
+struct RaySmem {
+    uint32_t bvh[kBvhWords];
+    AssetTable assets;
+    float agentPos[kMaxAgents][3];
+    float agentRot[kMaxAgents][4];
+    int agentSlot[kMaxAgents];
+    int agentType[kMaxAgents];
+    // visibility ray queue
+    float visDir[kMaxVisRays][3];
+    uint16_t visInfo[kMaxVisRays];        // agent k | target slot << 3 | seesHiderCandidate << 11
+    float *visOut[kMaxVisRays];
+    int numVis;
+};
+
+// Ray vs one leaf in object space; operand order of hs_trace.cuh::traceLeaf, tables in shared.
+__device__ __forceinline__ bool traceLeafS(const uint32_t *blob, const AssetTable &AT, int leaf,
+                                           Vec3 o, Vec3 d, float t_max, float *hit_t)
+{
+    const float *L = leafF(blob, leaf);
+    int obj = int(blob[kBvhLeafOff + leaf * kLeafWords + kLeafInfo] >> 8) & 0xFF;
+    Vec3 pos = {L[kLeafPos], L[kLeafPos + 1], L[kLeafPos + 2]};
+    Quat rot = {L[kLeafRot], L[kLeafRot + 1], L[kLeafRot + 2], L[kLeafRot + 3]};
+    Vec3 scale = {L[kLeafScale], L[kLeafScale + 1], L[kLeafScale + 2]};
+
+    Quat toLocal = qinv(rot);
+    Vec3 oo = rotate(toLocal, o - pos);
+    oo.x /= scale.x; oo.y /= scale.y; oo.z /= scale.z;
+    Vec3 od = rotate(toLocal, d);
+    od.x /= scale.x; od.y /= scale.y; od.z /= scale.z;
+    Vec3 inv = {1.f / od.x, 1.f / od.y, 1.f / od.z};
+
+    const ObjectData &O = AT.obj[obj];
+    Vec3 lo = {O.aabb[0], O.aabb[1], O.aabb[2]}, hi = {O.aabb[3], O.aabb[4], O.aabb[5]};
+    if (!aabbRayIntersects(lo, hi, oo, inv, 0.f, t_max)) return false;
+
+    if (O.primType == 4) {
+        float denom = od.z;
+        if (denom == 0.f) return false;
+        float t = -oo.z / denom;
+        if (t < 0.f || t > t_max) return false;
+        *hit_t = t;
+        return true;
+    }
+
+    const HullData &H = AT.hull[obj];
+    float tfirst = 0.f, tlast = t_max;
+    bool entered = false;
+    const int nf = H.numFaces;
+    for (int f = 0; f < nf; f++) {
+        Vec3 n = {H.planes[f][0], H.planes[f][1], H.planes[f][2]};
+        float pd = H.planes[f][3];
+        float denom = dot(n, od);
+        float negDist = pd - dot(n, oo);
+        if (denom == 0.0f) {
+            if (negDist < 0.0f) return false;
+        } else {
+            float t = negDist / denom;
+            if (denom < 0.0f) {
+                if (t >= tfirst) { tfirst = t; entered = true; }
+            } else {
+                if (t <= tlast) tlast = t;
+            }
+            if (tfirst > tlast) return false;
+        }
+    }
+    if (!entered) return false;
+    *hit_t = tfirst;
+    return true;
+}
+
+// Warp-convergent closest-hit query.  Must be called by all 32 lanes of a warp; lanes without
+// a ray pass active = false.  Returns the body slot of the closest hit or -1.
+__device__ inline int traceRayWarp(const uint32_t *blob, const AssetTable &AT, bool active,
+                                   Vec3 o, Vec3 d, float t_max, float *out_t)
+{
+    const Vec3 inv = {1.f / d.x, 1.f / d.y, 1.f / d.z};
+    uint8_t stack[24];
+    int sp = 0;
+    int cur = -1;             // node whose children are being scanned, -1: pop next
+    int ci = 0;               // next child index of cur
+    int hitBits = 0;          // children of cur whose slab test passes without the t_max clamp
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;    // slab entry distances of cur's children
+    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    int pending = -1;         // leaf waiting for the shared leaf phase
+    int hitLeaf = -1;
+    bool done = !active;
+    if (active) { stack[0] = 0; sp = 1; }
+
+    while (true) {
+        if (!done && pending < 0) {
+            if (cur < 0) {
+                if (sp == 0) {
+                    done = true;
+                } else {
+                    cur = stack[--sp];
+                    ci = 0;
+                    const float4 *nf = reinterpret_cast<const float4 *>(blob + kBvhNodeOff + cur * kNodeWords);
+                    const float4 lox = nf[0], loy = nf[1], loz = nf[2], hix = nf[3], hiy = nf[4], hiz = nf[5];
+                    const int4 ch = *reinterpret_cast<const int4 *>(blob + kBvhNodeOff + cur * kNodeWords + kNodeChild);
+                    c0 = ch.x; c1 = ch.y; c2 = ch.z; c3 = ch.w;
+                    hitBits = 0;
+#define HS_SLAB(i, LX, LY, LZ, HX, HY, HZ, A, C)                                              \
+                    {                                                                          \
+                        float tlx = inv.x * (LX - o.x), tly = inv.y * (LY - o.y), tlz = inv.z * (LZ - o.z); \
+                        float tux = inv.x * (HX - o.x), tuy = inv.y * (HY - o.y), tuz = inv.z * (HZ - o.z); \
+                        float mnx = fminf(tlx, tux), mny = fminf(tly, tuy), mnz = fminf(tlz, tuz);        \
+                        float mxx = fmaxf(tlx, tux), mxy = fmaxf(tly, tuy), mxz = fmaxf(tlz, tuz);        \
+                        A = fmaxf(mnx, fmaxf(mny, fmaxf(mnz, 0.f)));                           \
+                        float b = fminf(mxx, fminf(mxy, fminf(mxz, INFINITY)));                \
+                        if (C != kSentinel && A <= b) hitBits |= 1 << i;                       \
+                    }
+                    HS_SLAB(0, lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, a0, c0)
+                    HS_SLAB(1, lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, a1, c1)
+                    HS_SLAB(2, lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, a2, c2)
+                    HS_SLAB(3, lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, a3, c3)
+#undef HS_SLAB
+                }
+            }
+            if (cur >= 0) {
+                // scan children in order; stop at the first leaf that needs testing
+                while (ci < 4) {
+                    int i = ci++;
+                    if (!((hitBits >> i) & 1)) continue;
+                    float a = i == 0 ? a0 : (i == 1 ? a1 : (i == 2 ? a2 : a3));
+                    if (!(a <= t_max)) continue;
+                    int child = i == 0 ? c0 : (i == 1 ? c1 : (i == 2 ? c2 : c3));
+                    if (child < 0) { pending = child & 0x7FFFFFFF; break; }
+                    if (sp < 24) stack[sp++] = (uint8_t)child;
+                }
+                if (ci >= 4 && pending < 0) cur = -1;
+            }
+        }
+        const unsigned act = __ballot_sync(0xFFFFFFFFu, !done);
+        if (act == 0) break;
+        const unsigned pend = __ballot_sync(0xFFFFFFFFu, pending >= 0);
+        if (pend != 0 && (pend == act || __popc(pend) * 2 >= __popc(act))) {
+            if (pending >= 0) {
+                float t;
+                if (traceLeafS(blob, AT, pending, o, d, t_max, &t)) { t_max = t; hitLeaf = pending; }
+                pending = -1;
+                if (ci >= 4) cur = -1;
+            }
+        }
+    }
+    if (hitLeaf < 0) return -1;
+    *out_t = t_max;
+    return int(blob[kBvhLeafOff + hitLeaf * kLeafWords + kLeafInfo] & 0xFF);
+}
+
+__global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosThreshold)
+{
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    RaySmem &sm = *reinterpret_cast<RaySmem *>(smemRaw);
+    const int w = blockIdx.x;
+    const int tid = threadIdx.x;
+    const int A = S.p.agentsPerWorld;
+
+    // ---- stage the world's BVH tile + the asset table ---------------------------------------
+    const uint32_t *g = BVH(S, w);
+    const int numNodes = min((int)g[0], kMaxNodes), numLeaves = min((int)g[1], kMaxBodies);
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(g);
+        uint4 *dst = reinterpret_cast<uint4 *>(sm.bvh);
+        const int nodeVec = (kBvhNodeOff + numNodes * kNodeWords) / 4;
+        for (int i = tid; i < nodeVec; i += kRayThreads) dst[i] = src[i];
+        const int leafVec0 = kBvhLeafOff / 4, leafVec = (numLeaves * kLeafWords) / 4;
+        for (int i = tid; i < leafVec; i += kRayThreads) dst[leafVec0 + i] = src[leafVec0 + i];
+        const uint32_t *ca = reinterpret_cast<const uint32_t *>(&c_assets);
+        uint32_t *sa = reinterpret_cast<uint32_t *>(&sm.assets);
+        for (int i = tid; i < int(sizeof(AssetTable) / 4); i += kRayThreads) sa[i] = ca[i];
+    }
+    if (tid < A) {
+        int slot = WB(S, WB_IFACE_SLOT + tid, w);
+        sm.agentSlot[tid] = slot == 0xFF ? -1 : slot;
+        sm.agentType[tid] = WB(S, WB_IFACE_TYPE + tid, w);
+        if (slot != 0xFF) {
+            Vec3 p = loadPos(S, slot, w);
+            Quat q = loadRot(S, slot, w);
+            sm.agentPos[tid][0] = p.x; sm.agentPos[tid][1] = p.y; sm.agentPos[tid][2] = p.z;
+            sm.agentRot[tid][0] = q.w; sm.agentRot[tid][1] = q.x; sm.agentRot[tid][2] = q.y; sm.agentRot[tid][3] = q.z;
+        }
+    }
+    if (tid == 0) sm.numVis = 0;
+    __syncthreads();
+
+    // ---- visibility: cone test per (agent, target); survivors join the ray queue --------------
+    constexpr int kTargets = kMaxBoxes + kMaxRamps + kMaxAgents;      // 17 lanes of the old kernel
+    for (int e = tid; e < A * kTargets; e += kRayThreads) {
+        const int k = e / kTargets, lane = e % kTargets;
+        if (sm.agentSlot[k] < 0) continue;
+        const size_t row = size_t(w) * A + k;
+        float *out = nullptr;
+        int other = -1;
+        bool hiderTarget = false;
+        if (lane < kMaxBoxes) {
+            out = S.exBoxVis + row * kMaxBoxes + lane;
+            if (lane < WI(S, WF_NUM_BOXES, w)) other = WB(S, WB_BOX_SLOT + lane, w);
+        } else if (lane < kMaxBoxes + kMaxRamps) {
+            int i = lane - kMaxBoxes;
+            out = S.exRampVis + row * kMaxRamps + i;
+            if (i < WI(S, WF_NUM_RAMPS, w)) other = WB(S, WB_RAMP_SLOT + i, w);
+        } else {
+            int j = lane - kMaxBoxes - kMaxRamps;
+            int numAgents = WI(S, WF_NUM_AGENTS, w);
+            if (j == k && j < numAgents) continue;
+            int outIdx = j < numAgents ? otherAgentIndex(k, j) : j - 1;
+            if (outIdx < 0 || outIdx >= kMaxAgents - 1) continue;
+            out = S.exAgentVis + row * (kMaxAgents - 1) + outIdx;
+            if (j < numAgents) {
+                other = WB(S, WB_IFACE_SLOT + j, w);
+                hiderTarget = sm.agentType[k] == AGENT_SEEKER && WB(S, WB_IFACE_TYPE + j, w) == AGENT_HIDER;
+            }
+        }
+        if (other < 0) { *out = 0.f; continue; }
+        Vec3 apos = {sm.agentPos[k][0], sm.agentPos[k][1], sm.agentPos[k][2]};
+        Quat arot = {sm.agentRot[k][0], sm.agentRot[k][1], sm.agentRot[k][2], sm.agentRot[k][3]};
+        Vec3 afwd = rotate(arot, v3(0, 1, 0));
+        Vec3 to = loadPos(S, other, w) - apos;
+        float cosA = dot(normalize(to), afwd);
+        if (cosA < cosThreshold) { *out = 0.f; continue; }
+        int q = atomicAdd(&sm.numVis, 1);
+        sm.visDir[q][0] = to.x; sm.visDir[q][1] = to.y; sm.visDir[q][2] = to.z;
+        sm.visInfo[q] = uint16_t(k | (other << 3) | (hiderTarget ? 1 << 11 : 0));
+        sm.visOut[q] = out;
+    }
+    __syncthreads();
+
+    // ---- all rays of the world: [0, A*30) lidar, then the visibility queue ------------------
+    const int numLidar = A * 30;
+    const int numRays = numLidar + sm.numVis;
+    const int rounded = (numRays + 31) & ~31;
+    for (int r = tid; r < rounded; r += kRayThreads) {
+        bool active = r < numRays;
+        Vec3 o = {0.f, 0.f, 0.f}, d = {1.f, 0.f, 0.f};
+        float tmax = 0.f;
+        int k = 0, q = 0;
+        const bool isLidar = r < numLidar;
+        if (active) {
+            if (isLidar) {
+                k = r / 30;
+                const int i = r - k * 30;
+                if (sm.agentSlot[k] < 0) {
+                    active = false;
+                } else {
+                    Quat rot = {sm.agentRot[k][0], sm.agentRot[k][1], sm.agentRot[k][2], sm.agentRot[k][3]};
+                    Vec3 fwd = rotate(rot, v3(0, 1, 0));
+                    Vec3 right = rotate(rot, v3(1, 0, 0));
+                    float x = c_lidarDir[i][0], y = c_lidarDir[i][1];
+                    d = normalize(x * right + y * fwd);
+                    tmax = 200.f;
+                }
+            } else {
+                q = r - numLidar;
+                k = sm.visInfo[q] & 7;
+                d = {sm.visDir[q][0], sm.visDir[q][1], sm.visDir[q][2]};
+                tmax = 1.f;
+            }
+            o = {sm.agentPos[k][0], sm.agentPos[k][1], sm.agentPos[k][2]};
+        }
+        float t = 0.f;
+        int hit = traceRayWarp(sm.bvh, sm.assets, active, o, d, tmax, &t);
+        if (!active) continue;
+        if (isLidar) {
+            S.exLidar[(size_t(w) * A + k) * 30 + (r - k * 30)] = hit < 0 ? 0.f : t;
+        } else {
+            const int info = sm.visInfo[q];
+            const bool vis = hit == ((info >> 3) & 0xFF);
+            *sm.visOut[q] = vis ? 1.f : 0.f;
+            // CPU-backend side effect (src/sim.cpp:700-705)
+            if (vis && (info >> 11)) WI(S, WF_HIDER_REWARD, w) = __float_as_int(-1.f);
+        }
+    }
+}
+
+}  // namespace hs

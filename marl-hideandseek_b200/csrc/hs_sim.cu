@@ -21,6 +21,7 @@
 #include "hs_trace.cuh"
 #include "hs_agents.cuh"
 #include "hs_obs.cuh"
+#include "hs_rays.cuh"
 #include "hs_narrowphase.cuh"
 #include "hs_solver.cuh"
 #include "hs_checkpoint.cuh"
@@ -129,6 +130,19 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     buildAssetTable(T);
     HS_CUDA(cudaMemcpyToSymbol(c_assets, &T, sizeof(T)));
 
+    {
+        // lidar ray directions (src/sim.cpp:728-731), evaluated once with the shared detmath
+        float dirs[30][2];
+        const float pi = 3.14159265358979323846f;
+        for (int i = 0; i < 30; i++) {
+            float theta = 2.f * pi * (float(i) / float(30)) + pi / 2.f;
+            float sn, cs;
+            hs_det_sincosf(theta, &sn, &cs);
+            dirs[i][0] = cs; dirs[i][1] = sn;
+        }
+        HS_CUDA(cudaMemcpyToSymbol(c_lidarDir, dirs, sizeof(dirs)));
+        HS_CUDA(cudaFuncSetAttribute(k_rays, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
+    }
     HS_CUDA(cudaStreamCreateWithFlags(&sim->graphStream, cudaStreamNonBlocking));
     {
         // cosf(toRadians(135.f / 2.f)) as the reference's compiler folds it (src/sim.cpp:582,767)
@@ -305,8 +319,7 @@ void launchBroadphaseSetup(Launcher &L, bool mayRebuild)
 void launchObservations(Launcher &L, float cosThr)
 {
     k_observations<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.mark("k_observations");
-    k_visibility<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S, cosThr); L.mark("k_visibility");
-    k_lidar<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.mark("k_lidar");
+    k_rays<<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr); L.mark("k_rays");
     k_debug_positions<<<L.gWorld(), 128, 0, L.st>>>(L.S); L.mark("k_debug_positions");
 }
 
