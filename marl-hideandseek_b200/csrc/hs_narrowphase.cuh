@@ -316,96 +316,146 @@ __device__ inline Manifold edgeContact(const EdgeQuery &q, const WorldHull &a, c
     return m;
 }
 
-// runNarrowphase for one candidate; returns false when no contact is produced.
-__device__ inline bool narrowphasePair(const DeviceState &S, int w, int a, int b,
-                                       int *refOut, int *altOut, Manifold *out)
+// ---- kernel ------------------------------------------------------------------------------------
+// One CTA serves kNpWorlds consecutive worlds.  A world has only ~27 candidate pairs of two very
+// different costs (hull vs ground plane: one hull transform; hull vs hull: two transforms + SAT +
+// clipping), so a warp per world would run at a handful of active lanes.  Instead:
+//   pass 1 (8 lanes per world): load both poses, world-AABB reject (narrowphase.cpp:1560-1577),
+//           classify the survivors and append them to two CTA-wide shared lists (plane / hull);
+//   pass 2: the whole CTA drains the plane list, then the hull list — lanes are full and every
+//           warp runs one code path at a time.
+// Each pair still writes the contact slot of its own candidate index, so the solver sees
+// contacts in the reference's creation order no matter which lane produced them.
+constexpr int kNpWorlds = 16;
+constexpr int kNpThreads = 128;
+constexpr int kNpListCap = kNpWorlds * kMaxCand;
+
+struct NpSmem {
+    AssetTable assets;
+    uint32_t list[kNpListCap];      // plane pairs grow from the front, hull pairs from the back
+    int numPlane, numHull;
+};
+
+__device__ __forceinline__ AABB objAABBOf(const AssetTable &AT, int obj)
 {
-    uint32_t ma = META(S, a, w), mb = META(S, b, w);
-    int objA = metaObj(ma), objB = metaObj(mb);
-    int typeA = c_assets.obj[objA].primType, typeB = c_assets.obj[objB].primType;
-    if (typeA > typeB) {
-        int t = a; a = b; b = t;
-        t = objA; objA = objB; objB = t;
-        t = typeA; typeA = typeB; typeB = t;
-    }
-    Vec3 aPos = loadPos(S, a, w), bPos = loadPos(S, b, w);
-    Quat aRot = loadRot(S, a, w), bRot = loadRot(S, b, w);
-    Vec3 aScale = loadScale(S, a, w), bScale = loadScale(S, b, w);
-
-    AABB aBox = aabbApplyTRS(objAABB(objA), aPos, aRot, aScale);
-    AABB bBox = aabbApplyTRS(objAABB(objB), bPos, bRot, bScale);
-    if (!aabbIntersects(aBox, bBox)) return false;
-
-    if (typeA == 2 && typeB == 4) {
-        WorldHull ha;
-        makeWorldHull(ha, c_assets.hull[objA], aPos, aRot, aScale);
-        Vec3 n = rotate(bRot, v3(0, 0, 1));
-        Plane pl = {n, dot(n, bPos)};
-        if (hullDistanceFromPlane(pl, ha) > 0.0f) return false;
-        int inc = findIncidentFace(ha, pl.n);
-        Manifold m = facePlaneContact(pl, inc, ha);
-        if (m.n <= 0) return false;
-        *refOut = b; *altOut = a; *out = m;
-        return true;
-    }
-    if (typeA != 2 || typeB != 2) return false;   // sphere / plane-plane pairs never occur here
-
-    WorldHull ha, hb;
-    makeWorldHull(ha, c_assets.hull[objA], aPos, aRot, aScale);
-    makeWorldHull(hb, c_assets.hull[objB], bPos, bRot, bScale);
-
-    FaceQuery fa = queryFaces(ha, hb);
-    if (fa.sep > 0.0f) return false;
-    FaceQuery fb = queryFaces(hb, ha);
-    if (fb.sep > 0.0f) return false;
-    EdgeQuery eq = queryEdges(ha, hb);
-    if (eq.sep > 0.0f) return false;
-
-    bool faceA = fa.sep > eq.sep, faceB = fb.sep > eq.sep;
-    if (faceA || faceB) {
-        bool aIsRef = fa.sep >= fb.sep;
-        Plane ref = aIsRef ? fa.plane : fb.plane;
-        int refFace = aIsRef ? fa.face : fb.face;
-        const WorldHull &R = aIsRef ? ha : hb;
-        const WorldHull &O = aIsRef ? hb : ha;
-        int inc = findIncidentFace(O, ref.n);
-        Manifold m = faceContact(ref, refFace, inc, R, O);
-        if (m.n <= 0) return false;
-        *refOut = aIsRef ? a : b; *altOut = aIsRef ? b : a; *out = m;
-        return true;
-    }
-    *refOut = a; *altOut = b;
-    *out = edgeContact(eq, ha, hb);
-    return true;
+    const float *a = AT.obj[obj].aabb;
+    return {{a[0], a[1], a[2]}, {a[3], a[4], a[5]}};
 }
 
-// one warp per world, lanes stride over the world's candidates
-__global__ void k_narrowphase(DeviceState S)
+__device__ __forceinline__ void writeContact(const DeviceState &S, int w, int c, int ref, int alt, const Manifold &m)
 {
-    const int lane = threadIdx.x & 31;
-    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (w >= S.p.numWorlds) return;
-    const int nc = WI(S, WF_NUM_CAND, w);
-    const uint16_t *cand = S.cand + size_t(w) * kMaxCand;
-    for (int c = lane; c < nc; c += 32) {
-        uint16_t pr = cand[c];
-        int ref, alt;
-        Manifold m;
-        uint32_t meta = 0;
-        if (narrowphasePair(S, w, pr & 0xFF, pr >> 8, &ref, &alt, &m)) {
-            float *o = S.contact + (size_t(w) * kMaxCand + c) * kContactWords;
-            for (int i = 0; i < 4; i++) {
-                bool v = i < m.n;
-                o[i * 4 + 0] = v ? m.pts[i].x : 0.f;
-                o[i * 4 + 1] = v ? m.pts[i].y : 0.f;
-                o[i * 4 + 2] = v ? m.pts[i].z : 0.f;
-                o[i * 4 + 3] = v ? m.depth[i] : 0.f;
+    float4 *o = reinterpret_cast<float4 *>(S.contact + (size_t(w) * kMaxCand + c) * kContactWords);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        bool v = i < m.n;
+        o[i] = v ? make_float4(m.pts[i].x, m.pts[i].y, m.pts[i].z, m.depth[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    o[4] = make_float4(m.normal.x, m.normal.y, m.normal.z, 0.f);
+    S.cmeta[size_t(w) * kMaxCand + c] = uint32_t(ref) | (uint32_t(alt) << 8) | (uint32_t(m.n) << 16);
+}
+
+__global__ void __launch_bounds__(kNpThreads) k_narrowphase(DeviceState S)
+{
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    NpSmem &sm = *reinterpret_cast<NpSmem *>(smemRaw);
+    const int tid = threadIdx.x;
+    {
+        const uint32_t *ca = reinterpret_cast<const uint32_t *>(&c_assets);
+        uint32_t *sa = reinterpret_cast<uint32_t *>(&sm.assets);
+        for (int i = tid; i < int(sizeof(AssetTable) / 4); i += kNpThreads) sa[i] = ca[i];
+        if (tid == 0) { sm.numPlane = 0; sm.numHull = 0; }
+    }
+    __syncthreads();
+    const AssetTable &AT = sm.assets;
+    const int w0 = blockIdx.x * kNpWorlds;
+
+    // ---- pass 1: AABB reject + classification, 8 lanes per world ---------------------------------
+    {
+        constexpr int kLanes = kNpThreads / kNpWorlds;
+        const int wi = tid / kLanes, l = tid % kLanes;
+        const int w = w0 + wi;
+        const int nc = w < S.p.numWorlds ? WI(S, WF_NUM_CAND, w) : 0;
+        const uint16_t *cand = S.cand + size_t(w) * kMaxCand;
+        for (int c = l; c < nc; c += kLanes) {
+            uint16_t pr = cand[c];
+            int a = pr & 0xFF, b = pr >> 8;
+            int objA = metaObj(META(S, a, w)), objB = metaObj(META(S, b, w));
+            int typeA = AT.obj[objA].primType, typeB = AT.obj[objB].primType;
+            if (typeA > typeB) {
+                int t = a; a = b; b = t;
+                t = objA; objA = objB; objB = t;
+                t = typeA; typeA = typeB; typeB = t;
             }
-            o[16] = m.normal.x; o[17] = m.normal.y; o[18] = m.normal.z;
-            o[19] = 0.f;
-            meta = uint32_t(ref) | (uint32_t(alt) << 8) | (uint32_t(m.n) << 16);
+            AABB aBox = aabbApplyTRS(objAABBOf(AT, objA), loadPos(S, a, w), loadRot(S, a, w), loadScale(S, a, w));
+            AABB bBox = aabbApplyTRS(objAABBOf(AT, objB), loadPos(S, b, w), loadRot(S, b, w), loadScale(S, b, w));
+            bool plane = typeA == 2 && typeB == 4, hull = typeA == 2 && typeB == 2;
+            if (!aabbIntersects(aBox, bBox) || !(plane || hull)) {
+                S.cmeta[size_t(w) * kMaxCand + c] = 0;
+                continue;
+            }
+            uint32_t rec = uint32_t(wi) | (uint32_t(c) << 4) | (uint32_t(a) << 12) | (uint32_t(b) << 20);
+            if (plane) sm.list[atomicAdd(&sm.numPlane, 1)] = rec;
+            else sm.list[kNpListCap - 1 - atomicAdd(&sm.numHull, 1)] = rec;
         }
-        S.cmeta[size_t(w) * kMaxCand + c] = meta;
+    }
+    __syncthreads();
+
+    // ---- pass 2a: hull vs ground plane -------------------------------------------------------------
+    const int numPlane = sm.numPlane, numHull = sm.numHull;
+    for (int i = tid; i < numPlane; i += kNpThreads) {
+        const uint32_t rec = sm.list[i];
+        const int w = w0 + int(rec & 15), c = int(rec >> 4) & 0xFF, a = int(rec >> 12) & 0xFF, b = int(rec >> 20) & 0xFF;
+        WorldHull ha;
+        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], loadPos(S, a, w), loadRot(S, a, w), loadScale(S, a, w));
+        Vec3 n = rotate(loadRot(S, b, w), v3(0, 0, 1));
+        Plane pl = {n, dot(n, loadPos(S, b, w))};
+        bool has = false;
+        Manifold m;
+        if (!(hullDistanceFromPlane(pl, ha) > 0.0f)) {
+            int inc = findIncidentFace(ha, pl.n);
+            m = facePlaneContact(pl, inc, ha);
+            has = m.n > 0;
+        }
+        if (has) writeContact(S, w, c, b, a, m);
+        else S.cmeta[size_t(w) * kMaxCand + c] = 0;
+    }
+
+    // ---- pass 2b: hull vs hull -----------------------------------------------------------------------
+    for (int i = tid; i < numHull; i += kNpThreads) {
+        const uint32_t rec = sm.list[kNpListCap - 1 - i];
+        const int w = w0 + int(rec & 15), c = int(rec >> 4) & 0xFF, a = int(rec >> 12) & 0xFF, b = int(rec >> 20) & 0xFF;
+        WorldHull ha, hb;
+        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], loadPos(S, a, w), loadRot(S, a, w), loadScale(S, a, w));
+        makeWorldHull(hb, AT.hull[metaObj(META(S, b, w))], loadPos(S, b, w), loadRot(S, b, w), loadScale(S, b, w));
+        bool has = false;
+        int ref = a, alt = b;
+        Manifold m;
+        do {
+            FaceQuery fa = queryFaces(ha, hb);
+            if (fa.sep > 0.0f) break;
+            FaceQuery fb = queryFaces(hb, ha);
+            if (fb.sep > 0.0f) break;
+            EdgeQuery eq = queryEdges(ha, hb);
+            if (eq.sep > 0.0f) break;
+            bool faceA = fa.sep > eq.sep, faceB = fb.sep > eq.sep;
+            if (faceA || faceB) {
+                bool aIsRef = fa.sep >= fb.sep;
+                Plane rp = aIsRef ? fa.plane : fb.plane;
+                int refFace = aIsRef ? fa.face : fb.face;
+                const WorldHull &R = aIsRef ? ha : hb;
+                const WorldHull &O = aIsRef ? hb : ha;
+                int inc = findIncidentFace(O, rp.n);
+                m = faceContact(rp, refFace, inc, R, O);
+                if (m.n <= 0) break;
+                ref = aIsRef ? a : b; alt = aIsRef ? b : a;
+                has = true;
+            } else {
+                m = edgeContact(eq, ha, hb);
+                has = true;
+            }
+        } while (false);
+        if (has) writeContact(S, w, c, ref, alt, m);
+        else S.cmeta[size_t(w) * kMaxCand + c] = 0;
     }
 }
 

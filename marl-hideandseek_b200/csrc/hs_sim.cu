@@ -332,10 +332,10 @@ void launchStep(Launcher &L, float cosThr)
     k_broadphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.mark("k_broadphase");
     for (int i = 0; i < kSubsteps; i++) {
         k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep");
-        k_narrowphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.mark("k_narrowphase");
-        k_solve_positions<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_solve_positions");
+        k_narrowphase<<<(L.N() + kNpWorlds - 1) / kNpWorlds, kNpThreads, sizeof(NpSmem), L.st>>>(L.S); L.mark("k_narrowphase");
+        k_solve_positions<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_positions");
         k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_set_velocities");
-        k_solve_velocities<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_solve_velocities");
+        k_solve_velocities<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_velocities");
     }
     k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_leaf_update");
     k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_refit");
@@ -576,12 +576,6 @@ extern "C" int hs_world_stats(hs_sim *sim, int64_t *out4)
     HS_TRY(sumRow(WF_NUM_BODIES, row, &out4[0]));
     HS_TRY(sumRow(WF_NUM_AGENTS, row, &out4[1]));
     HS_TRY(sumRow(WF_NUM_CAND, ncand, &out4[2]));
-    std::vector<uint32_t> cm(N * kMaxCand);
-    HS_CUDA(cudaMemcpy(cm.data(), sim->S.cmeta, cm.size() * 4, cudaMemcpyDeviceToHost));
-    int64_t k = 0;
-    for (size_t w = 0; w < N; w++)
-        for (int c = 0; c < ncand[w]; c++)
-            if (cm[w * kMaxCand + c] >> 16) k++;
-    out4[3] = k;
+    HS_TRY(sumRow(WF_NUM_CONTACTS, row, &out4[3]));
     return 0;
 }

@@ -166,7 +166,8 @@ __device__ __forceinline__ void localContacts(Vec3 px1, Quat pq1, Vec3 px2, Quat
     *r2 = rotate(qinv(pq2), contact2 - px2);
 }
 
-__device__ inline void handleContact(const DeviceState &S, int w, uint32_t meta, float *cdata)
+__device__ inline void handleContact(const DeviceState &S, int w, uint32_t meta, float *cdata,
+                                     bool write1, bool write2)
 {
     const int b1 = meta & 0xFF, b2 = (meta >> 8) & 0xFF;
     ContactView c = loadContact(cdata, meta);
@@ -211,8 +212,8 @@ __device__ inline void handleContact(const DeviceState &S, int w, uint32_t meta,
     }
     cdata[19] = lambda_n;
 
-    storeV3(S, BF_PX, b1, w, x1); storeV3(S, BF_PX, b2, w, x2);
-    storeQ(S, BF_QW, b1, w, q1); storeQ(S, BF_QW, b2, w, q2);
+    if (write1) { storeV3(S, BF_PX, b1, w, x1); storeQ(S, BF_QW, b1, w, q1); }
+    if (write2) { storeV3(S, BF_PX, b2, w, x2); storeQ(S, BF_QW, b2, w, q2); }
 }
 
 __device__ inline void handleFixedJoint(const DeviceState &S, int w, int k, int b1, int b2)
@@ -266,33 +267,120 @@ __device__ inline void handleFixedJoint(const DeviceState &S, int w, int k, int 
     storeQ(S, BF_QW, b1, w, q1); storeQ(S, BF_QW, b2, w, q2);
 }
 
-// solvePositions: one thread per world
-__global__ void k_solve_positions(DeviceState S)
+// ---- ordered Gauss-Seidel without one-thread-per-world serialisation -----------------------------
+// The reference solves contacts strictly in creation order (xpbd.cpp:724-735).  Contact i only
+// depends on an earlier contact if they share a body whose state the pass can change, so each
+// world's contacts are assigned a level = 1 + the level of the latest earlier contact sharing
+// such a body, and a group of kSolveLanes lanes sweeps the levels, one contact per lane.
+// Contacts inside a level touch disjoint mutable bodies: every read sees exactly the value the
+// sequential order would produce, so results are bit-identical to the serial solver.  Bodies
+// the pass cannot change carry no dependency and are never written: position pass — Static
+// bodies with identity rotation (walls, ground plane; a rotated Static body still has its
+// quaternion re-normalised by the reference); velocity pass — every Static body (inverse mass
+// and inertia are zero).  4 worlds share a warp, so lanes stay busy although one world has
+// only a handful of contacts per level.
+constexpr int kSolveLanes = 8;
+constexpr int kSolveThreads = 128;
+constexpr int kSolveGroups = kSolveThreads / kSolveLanes;
+
+struct SolveGroupSmem {
+    uint32_t cm[kMaxCand];       // compacted contact meta, creation order
+    uint8_t cslot[kMaxCand];     // candidate slot of compacted contact k
+    uint8_t clvl[kMaxCand];
+    uint8_t blvl[kMaxBodies + 4];
+};
+
+// Compacts the world's contacts (candidate order), assigns levels; returns K and the top level.
+template <bool kVelocityPass>
+__device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGroupSmem &g, int lg, unsigned gmask,
+                                           int gshift, int *maxLvlOut)
 {
-    int w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= S.p.numWorlds) return;
     const int nc = WI(S, WF_NUM_CAND, w);
-    for (int c = 0; c < nc; c++) {
-        uint32_t meta = S.cmeta[size_t(w) * kMaxCand + c];
-        if ((meta >> 16) == 0) continue;
-        handleContact(S, w, meta, S.contact + (size_t(w) * kMaxCand + c) * kContactWords);
+    const int nb = WI(S, WF_NUM_BODIES, w);
+    const uint32_t *cmeta = S.cmeta + size_t(w) * kMaxCand;
+    int K = 0;
+    for (int c0 = 0; c0 < nc; c0 += kSolveLanes) {
+        const int c = c0 + lg;
+        uint32_t m = c < nc ? cmeta[c] : 0u;
+        const bool has = (m >> 16) != 0;
+        const unsigned bal = (__ballot_sync(gmask, has) >> gshift) & ((1u << kSolveLanes) - 1u);
+        if (has) {
+            int k = K + __popc(bal & ((1u << lg) - 1u));
+            g.cm[k] = m;
+            g.cslot[k] = (uint8_t)c;
+        }
+        K += __popc(bal);
+    }
+    for (int s = lg; s < nb; s += kSolveLanes) {
+        uint32_t m = META(S, s, w);
+        bool fixedBody = metaResp(m) == RESP_STATIC;
+        if (!kVelocityPass)
+            fixedBody = fixedBody && BF(S, BF_QW, s, w) == 1.f && BF(S, BF_QX, s, w) == 0.f &&
+                        BF(S, BF_QY, s, w) == 0.f && BF(S, BF_QZ, s, w) == 0.f;
+        g.blvl[s] = fixedBody ? 0xFF : 0;
+    }
+    __syncwarp(gmask);
+    int maxLvl = 0;
+    if (lg == 0) {
+        for (int k = 0; k < K; k++) {
+            uint32_t cm = g.cm[k];
+            int b1 = cm & 0xFF, b2 = (cm >> 8) & 0xFF;
+            int l1 = g.blvl[b1], l2 = g.blvl[b2];
+            int lv = max(l1 == 0xFF ? 0 : l1, l2 == 0xFF ? 0 : l2);
+            g.clvl[k] = (uint8_t)lv;
+            if (l1 != 0xFF) g.blvl[b1] = (uint8_t)(lv + 1);
+            if (l2 != 0xFF) g.blvl[b2] = (uint8_t)(lv + 1);
+            maxLvl = max(maxLvl, lv);
+        }
+    }
+    maxLvl = __shfl_sync(gmask, maxLvl, gshift);
+    __syncwarp(gmask);
+    *maxLvlOut = maxLvl;
+    return K;
+}
+
+// solvePositions
+__global__ void __launch_bounds__(kSolveThreads) k_solve_positions(DeviceState S)
+{
+    __shared__ SolveGroupSmem sg[kSolveGroups];
+    const int lane = threadIdx.x & 31;
+    const int lg = lane % kSolveLanes;
+    const int gshift = lane - lg;
+    const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
+    const int w = blockIdx.x * kSolveGroups + threadIdx.x / kSolveLanes;
+    if (w >= S.p.numWorlds) return;
+    SolveGroupSmem &g = sg[threadIdx.x / kSolveLanes];
+
+    int maxLvl;
+    const int K = buildLevels<false>(S, w, g, lg, gmask, gshift, &maxLvl);
+    float *contacts = S.contact + size_t(w) * kMaxCand * kContactWords;
+    for (int lv = 0; lv <= maxLvl; lv++) {
+        for (int k = lg; k < K; k += kSolveLanes) {
+            if (g.clvl[k] != lv) continue;
+            uint32_t cm = g.cm[k];
+            handleContact(S, w, cm, contacts + size_t(g.cslot[k]) * kContactWords,
+                          g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
+        }
+        __syncwarp(gmask);
     }
 
-    // joints in creation order
-    const int na = WI(S, WF_NUM_AGENTS, w);
-    const int nDyn = WI(S, WF_NUM_DYN, w);
-    int lastSeq = -1;
-    for (int it = 0; it < na; it++) {
-        int best = -1, bestSeq = 0x7FFFFFFF;
-        for (int k = 0; k < na; k++) {
-            uint32_t jm = JMETA(S, k, w);
-            if (jm == 0xFFFFFFFFu) continue;
-            int seq = int(jm >> 16);
-            if (seq > lastSeq && seq < bestSeq) { bestSeq = seq; best = k; }
+    // joints in creation order (at most one Fixed joint per agent; rare)
+    if (lg == 0) {
+        const int na = WI(S, WF_NUM_AGENTS, w);
+        const int nDyn = WI(S, WF_NUM_DYN, w);
+        int lastSeq = -1;
+        for (int it = 0; it < na; it++) {
+            int best = -1, bestSeq = 0x7FFFFFFF;
+            for (int k = 0; k < na; k++) {
+                uint32_t jm = JMETA(S, k, w);
+                if (jm == 0xFFFFFFFFu) continue;
+                int seq = int(jm >> 16);
+                if (seq > lastSeq && seq < bestSeq) { bestSeq = seq; best = k; }
+            }
+            if (best < 0) break;
+            lastSeq = bestSeq;
+            handleFixedJoint(S, w, best, nDyn + best, int(JMETA(S, best, w) & 0xFF));
         }
-        if (best < 0) break;
-        lastSeq = bestSeq;
-        handleFixedJoint(S, w, best, nDyn + best, int(JMETA(S, best, w) & 0xFF));
     }
 }
 
@@ -321,7 +409,8 @@ __device__ __forceinline__ Vec3 relVel(Vec3 v1, Vec3 v2, Vec3 o1, Vec3 o2, Vec3 
     return (v1 + cross(o1, d1)) - (v2 + cross(o2, d2));
 }
 
-__device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_t meta, const float *cdata)
+__device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_t meta, const float *cdata,
+                                            bool write1, bool write2)
 {
     const int b1 = meta & 0xFF, b2 = (meta >> 8) & 0xFF;
     ContactView c = loadContact(cdata, meta);
@@ -400,21 +489,35 @@ __device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_
         o2 -= rotate(q2, imp * fr2);
     }
 
-    storeV3(S, BF_VX, b1, w, v1); storeV3(S, BF_WX, b1, w, o1);
-    storeV3(S, BF_VX, b2, w, v2); storeV3(S, BF_WX, b2, w, o2);
+    if (write1) { storeV3(S, BF_VX, b1, w, v1); storeV3(S, BF_WX, b1, w, o1); }
+    if (write2) { storeV3(S, BF_VX, b2, w, v2); storeV3(S, BF_WX, b2, w, o2); }
 }
 
-// solveVelocities: one thread per world
-__global__ void k_solve_velocities(DeviceState S)
+// solveVelocities
+__global__ void __launch_bounds__(kSolveThreads) k_solve_velocities(DeviceState S)
 {
-    int w = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ SolveGroupSmem sg[kSolveGroups];
+    const int lane = threadIdx.x & 31;
+    const int lg = lane % kSolveLanes;
+    const int gshift = lane - lg;
+    const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
+    const int w = blockIdx.x * kSolveGroups + threadIdx.x / kSolveLanes;
     if (w >= S.p.numWorlds) return;
-    const int nc = WI(S, WF_NUM_CAND, w);
-    for (int c = 0; c < nc; c++) {
-        uint32_t meta = S.cmeta[size_t(w) * kMaxCand + c];
-        if ((meta >> 16) == 0) continue;
-        solveContactVelocity(S, w, meta, S.contact + (size_t(w) * kMaxCand + c) * kContactWords);
+    SolveGroupSmem &g = sg[threadIdx.x / kSolveLanes];
+
+    int maxLvl;
+    const int K = buildLevels<true>(S, w, g, lg, gmask, gshift, &maxLvl);
+    const float *contacts = S.contact + size_t(w) * kMaxCand * kContactWords;
+    for (int lv = 0; lv <= maxLvl; lv++) {
+        for (int k = lg; k < K; k += kSolveLanes) {
+            if (g.clvl[k] != lv) continue;
+            uint32_t cm = g.cm[k];
+            solveContactVelocity(S, w, cm, contacts + size_t(g.cslot[k]) * kContactWords,
+                                 g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
+        }
+        __syncwarp(gmask);
     }
+    if (lg == 0) WI(S, WF_NUM_CONTACTS, w) = K;
 }
 
 }  // namespace hs

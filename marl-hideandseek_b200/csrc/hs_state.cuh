@@ -90,6 +90,7 @@ enum WorldField : int {
     WF_JOINT_SEQ,                       // joint creation counter
     WF_NUM_CAND,
     WF_DID_RESET,                       // set by the reset stage for this step
+    WF_NUM_CONTACTS,                    // contacts of the last substep (statistics)
     WF_COUNT
 };
 
