@@ -144,63 +144,4 @@ __global__ void k_action(DeviceState S)
     }
 }
 
-// rewardsVisSystem + outputRewardsDonesSystem + updateEpisodeResultsSystem:
-// one thread per world (three short per-world passes that share hiderTeamReward).
-__global__ void k_rewards(DeviceState S, float cosThreshold)
-{
-    int w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= S.p.numWorlds) return;
-    const int A = S.p.agentsPerWorld;
-    const uint32_t *blob = BVH(S, w);
-    const int curStep = WI(S, WF_EPISODE_STEP, w);
-    float teamReward = __int_as_float(WI(S, WF_HIDER_REWARD, w));
-    const int numHiders = WI(S, WF_NUM_HIDERS, w);
-
-    for (int k = 0; k < A; k++) {
-        int slot = WB(S, WB_IFACE_SLOT + k, w);
-        if (slot == 0xFF || WB(S, WB_IFACE_TYPE + k, w) != AGENT_SEEKER) continue;
-        Vec3 spos = loadPos(S, slot, w);
-        Vec3 sfwd = rotate(loadRot(S, slot, w), v3(0, 1, 0));
-        for (int i = 0; i < numHiders; i++) {
-            int hslot = WB(S, WB_HIDER_SLOT + i, w);
-            Vec3 toHider = loadPos(S, hslot, w) - spos;
-            float cosA = dot(normalize(toHider), sfwd);
-            if (cosA < cosThreshold) continue;
-            float t;
-            if (traceRay(blob, spos, toHider, 1.f, &t) == hslot) { teamReward = -1.f; break; }
-        }
-    }
-    WI(S, WF_HIDER_REWARD, w) = __float_as_int(teamReward);
-
-    for (int k = 0; k < A; k++) {
-        int slot = WB(S, WB_IFACE_SLOT + k, w);
-        if (slot == 0xFF) continue;
-        size_t row = size_t(w) * A + k;
-        if (curStep == 0) S.exDone[row] = 0;
-        if (curStep < kNumPrepSteps - 1) { S.exReward[row] = 0.f; continue; }
-        if (curStep == kEpisodeLen - 1) S.exDone[row] = 1;
-        float r = teamReward;
-        if (WB(S, WB_IFACE_TYPE + k, w) == AGENT_SEEKER) r *= -1.f;
-        Vec3 pos = loadPos(S, slot, w);
-        if (fabsf(pos.x) >= 18.f || fabsf(pos.y) >= 18.f) r -= 10.f;
-        S.exReward[row] = r;
-    }
-
-    float *res = S.exEpisodeResult + size_t(w) * 2;
-    int s0 = WI(S, WF_SCORE0, w), s1 = WI(S, WF_SCORE1, w);
-    if (curStep == 0) { res[0] = 0.f; res[1] = 0.f; s0 = 0; s1 = 0; }
-    if (curStep >= kNumPrepSteps) {
-        bool seekersFirst = WI(S, WF_SEEKERS_FIRST, w) != 0;
-        bool hidden = teamReward == 1.f;
-        if (hidden == seekersFirst) s1 += 1; else s0 += 1;
-    }
-    if (curStep == kEpisodeLen - 1) {
-        if (s0 > s1) { res[0] = 1.f; res[1] = 0.f; }
-        else if (s0 < s1) { res[0] = 0.f; res[1] = 1.f; }
-        else { res[0] = 0.5f; res[1] = 0.5f; }
-    }
-    WI(S, WF_SCORE0, w) = s0;
-    WI(S, WF_SCORE1, w) = s1;
-}
-
 }  // namespace hs

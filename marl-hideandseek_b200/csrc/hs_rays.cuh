@@ -302,4 +302,82 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
     }
 }
 
+// rewardsVisSystem + outputRewardsDonesSystem + updateEpisodeResultsSystem (src/sim.cpp:763-893).
+// One warp per world: lane = (seeker, hider) pair for the occlusion rays — the reference's early
+// `break` only skips work, "any seeker sees any hider" is order-free — then lanes < A write the
+// per-agent reward / done rows and lane 0 the per-world episode result.
+constexpr int kRewardWarps = 4;
+
+__global__ void __launch_bounds__(kRewardWarps * 32) k_rewards(DeviceState S, float cosThreshold)
+{
+    __shared__ AssetTable s_assets;
+    {
+        const uint32_t *ca = reinterpret_cast<const uint32_t *>(&c_assets);
+        uint32_t *sa = reinterpret_cast<uint32_t *>(&s_assets);
+        for (int i = threadIdx.x; i < int(sizeof(AssetTable) / 4); i += blockDim.x) sa[i] = ca[i];
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int w = blockIdx.x * kRewardWarps + (threadIdx.x >> 5);
+    if (w >= S.p.numWorlds) return;
+    const int A = S.p.agentsPerWorld;
+    const int curStep = WI(S, WF_EPISODE_STEP, w);
+    float teamReward = __int_as_float(WI(S, WF_HIDER_REWARD, w));
+    const int numHiders = WI(S, WF_NUM_HIDERS, w), numSeekers = WI(S, WF_NUM_SEEKERS, w);
+
+    bool active = lane < numHiders * numSeekers;
+    int hslot = -1;
+    Vec3 spos = {0.f, 0.f, 0.f}, toHider = {1.f, 0.f, 0.f};
+    if (active) {
+        int si = lane / numHiders, hi = lane - si * numHiders;
+        int sslot = WB(S, WB_SEEKER_SLOT + si, w);
+        hslot = WB(S, WB_HIDER_SLOT + hi, w);
+        spos = loadPos(S, sslot, w);
+        Vec3 sfwd = rotate(loadRot(S, sslot, w), v3(0, 1, 0));
+        toHider = loadPos(S, hslot, w) - spos;
+        float cosA = dot(normalize(toHider), sfwd);
+        if (cosA < cosThreshold) active = false;
+    }
+    float t;
+    int hit = traceRayWarp(BVH(S, w), s_assets, active, spos, toHider, 1.f, &t);
+    if (__ballot_sync(0xFFFFFFFFu, active && hit == hslot)) teamReward = -1.f;
+
+    if (lane < A) {
+        const int k = lane;
+        int slot = WB(S, WB_IFACE_SLOT + k, w);
+        if (slot != 0xFF) {
+            size_t row = size_t(w) * A + k;
+            if (curStep == 0) S.exDone[row] = 0;
+            if (curStep < kNumPrepSteps - 1) {
+                S.exReward[row] = 0.f;
+            } else {
+                if (curStep == kEpisodeLen - 1) S.exDone[row] = 1;
+                float r = teamReward;
+                if (WB(S, WB_IFACE_TYPE + k, w) == AGENT_SEEKER) r *= -1.f;
+                Vec3 pos = loadPos(S, slot, w);
+                if (fabsf(pos.x) >= 18.f || fabsf(pos.y) >= 18.f) r -= 10.f;
+                S.exReward[row] = r;
+            }
+        }
+    }
+    if (lane == 0) {
+        WI(S, WF_HIDER_REWARD, w) = __float_as_int(teamReward);
+        float *res = S.exEpisodeResult + size_t(w) * 2;
+        int s0 = WI(S, WF_SCORE0, w), s1 = WI(S, WF_SCORE1, w);
+        if (curStep == 0) { res[0] = 0.f; res[1] = 0.f; s0 = 0; s1 = 0; }
+        if (curStep >= kNumPrepSteps) {
+            bool seekersFirst = WI(S, WF_SEEKERS_FIRST, w) != 0;
+            bool hidden = teamReward == 1.f;
+            if (hidden == seekersFirst) s1 += 1; else s0 += 1;
+        }
+        if (curStep == kEpisodeLen - 1) {
+            if (s0 > s1) { res[0] = 1.f; res[1] = 0.f; }
+            else if (s0 < s1) { res[0] = 0.f; res[1] = 1.f; }
+            else { res[0] = 0.5f; res[1] = 0.5f; }
+        }
+        WI(S, WF_SCORE0, w) = s0;
+        WI(S, WF_SCORE1, w) = s1;
+    }
+}
+
 }  // namespace hs

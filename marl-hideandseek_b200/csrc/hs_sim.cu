@@ -329,7 +329,7 @@ void launchStep(Launcher &L, float cosThr)
     k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.mark("k_move");
     launchBroadphaseSetup(L, true);
     k_action<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_action");
-    k_broadphase<<<L.gWarpWorld(), 128, 0, L.st>>>(L.S); L.mark("k_broadphase");
+    k_broadphase<<<(L.N() + kBroadWarps - 1) / kBroadWarps, kBroadWarps * 32, 0, L.st>>>(L.S); L.mark("k_broadphase");
     for (int i = 0; i < kSubsteps; i++) {
         k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep");
         k_narrowphase<<<(L.N() + kNpWorlds - 1) / kNpWorlds, kNpThreads, sizeof(NpSmem), L.st>>>(L.S); L.mark("k_narrowphase");
@@ -342,7 +342,7 @@ void launchStep(Launcher &L, float cosThr)
     if (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) {
         k_zero_agent_vel<<<dim3((L.N() * kMaxAgents + 127) / 128), 128, 0, L.st>>>(L.S); L.mark("k_zero_agent_vel");
     }
-    k_rewards<<<L.gWorld(64), 64, 0, L.st>>>(L.S, cosThr); L.mark("k_rewards");
+    k_rewards<<<(L.N() + kRewardWarps - 1) / kRewardWarps, kRewardWarps * 32, 0, L.st>>>(L.S, cosThr); L.mark("k_rewards");
     k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_reset");
     launchBroadphaseSetup(L, true);
     launchObservations(L, cosThr);

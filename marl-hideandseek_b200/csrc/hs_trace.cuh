@@ -134,19 +134,66 @@ __device__ __forceinline__ void forEachOverlap(const uint32_t *blob, const AABB 
     }
 }
 
-// findIntersectingEntry: one warp per world, lanes own bodies {lane, lane+32}.
-// Pass 1 counts each body's emitted pairs, a warp scan turns counts into
-// offsets in body-row order, pass 2 re-walks and writes — so the candidate list
-// is in exactly the order the sequential reference produces it.
-__global__ void k_broadphase(DeviceState S)
+// findIntersectingEntry: one warp per world, lanes own bodies {lane, lane+32}.  The world's BVH
+// nodes, leaf->slot map and body meta words are staged in shared memory (one coalesced copy)
+// because every lane walks the same small tree.  Pass 1 counts each body's emitted pairs, a
+// warp scan turns counts into offsets in body-row order, pass 2 re-walks and writes — so the
+// candidate list is in exactly the order the sequential reference produces it.
+constexpr int kBroadWarps = 4;
+
+struct alignas(16) BroadWarpSmem {
+    uint32_t nodes[kBvhNodeOff + kMaxNodes * kNodeWords];    // header + nodes, blob layout
+    uint32_t meta[kMaxBodies];
+    uint8_t leafSlot[kMaxBodies + 4];
+};
+
+template <typename Fn>
+__device__ __forceinline__ void forEachOverlapS(const BroadWarpSmem &ws, const AABB &q, Fn &&fn)
 {
+    uint8_t stack[24];
+    stack[0] = 0;
+    int sp = 1;
+    while (sp > 0) {
+        int node = stack[--sp];
+        const float4 *nf = reinterpret_cast<const float4 *>(ws.nodes + kBvhNodeOff + node * kNodeWords);
+        const float4 lox = nf[0], loy = nf[1], loz = nf[2], hix = nf[3], hiy = nf[4], hiz = nf[5];
+        const int4 ch = *reinterpret_cast<const int4 *>(ws.nodes + kBvhNodeOff + node * kNodeWords + kNodeChild);
+#define HS_OVL(C, LX, LY, LZ, HX, HY, HZ)                                                     \
+        if (C != kSentinel && q.lo.x < HX && LX < q.hi.x && q.lo.y < HY && LY < q.hi.y &&     \
+            q.lo.z < HZ && LZ < q.hi.z) {                                                      \
+            if (C < 0) fn(int(ws.leafSlot[C & 0x7FFFFFFF]));                                   \
+            else if (sp < 24) stack[sp++] = (uint8_t)C;                                        \
+        }
+        HS_OVL(ch.x, lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x)
+        HS_OVL(ch.y, lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y)
+        HS_OVL(ch.z, lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z)
+        HS_OVL(ch.w, lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w)
+#undef HS_OVL
+    }
+}
+
+__global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
+{
+    __shared__ __align__(16) BroadWarpSmem sm[kBroadWarps];
     const int lane = threadIdx.x & 31;
-    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int w = blockIdx.x * kBroadWarps + (threadIdx.x >> 5);
     if (w >= S.p.numWorlds) return;
+    BroadWarpSmem &ws = sm[threadIdx.x >> 5];
 
     const uint32_t *blob = BVH(S, w);
     const int nb = WI(S, WF_NUM_BODIES, w);
     const int N = S.p.numWorlds;
+    {
+        const int numNodes = min((int)blob[0], kMaxNodes), numLeaves = min((int)blob[1], kMaxBodies);
+        const uint4 *src = reinterpret_cast<const uint4 *>(blob);
+        uint4 *dst = reinterpret_cast<uint4 *>(ws.nodes);
+        const int nvec = (kBvhNodeOff + numNodes * kNodeWords) / 4;
+        for (int i = lane; i < nvec; i += 32) dst[i] = src[i];
+        for (int l = lane; l < numLeaves; l += 32)
+            ws.leafSlot[l] = (uint8_t)(blob[kBvhLeafOff + l * kLeafWords + kLeafInfo] & 0xFF);
+        for (int s = lane; s < nb; s += 32) ws.meta[s] = S.meta[size_t(s) * N + w];
+    }
+    __syncwarp();
 
     int counts[2] = {0, 0};
     uint32_t metas[2];
@@ -154,15 +201,15 @@ __global__ void k_broadphase(DeviceState S)
     for (int r = 0; r < 2; r++) {
         int s = lane + 32 * r;
         if (s >= nb) continue;
-        uint32_t m = S.meta[size_t(s) * N + w];
+        uint32_t m = ws.meta[s];
         metas[r] = m;
         const float *L = leafF(blob, metaLeaf(m));
         boxes[r] = {{L[0], L[1], L[2]}, {L[3], L[4], L[5]}};
         int eid = metaEid(m);
         bool aStatic = metaResp(m) == RESP_STATIC;
         int c = 0;
-        forEachOverlap(blob, boxes[r], [&](int other) {
-            uint32_t mo = S.meta[size_t(other) * N + w];
+        forEachOverlapS(ws, boxes[r], [&](int other) {
+            uint32_t mo = ws.meta[other];
             if (eid < metaEid(mo) && !(aStatic && metaResp(mo) == RESP_STATIC)) c++;
         });
         counts[r] = c;
@@ -197,8 +244,8 @@ __global__ void k_broadphase(DeviceState S)
         int eid = metaEid(m);
         bool aStatic = metaResp(m) == RESP_STATIC;
         int o = offs[r];
-        forEachOverlap(blob, boxes[r], [&](int other) {
-            uint32_t mo = S.meta[size_t(other) * N + w];
+        forEachOverlapS(ws, boxes[r], [&](int other) {
+            uint32_t mo = ws.meta[other];
             if (eid < metaEid(mo) && !(aStatic && metaResp(mo) == RESP_STATIC)) {
                 if (o < kMaxCand) out[o] = uint16_t(s | (other << 8));
                 o++;
