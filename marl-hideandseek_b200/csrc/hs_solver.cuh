@@ -280,13 +280,15 @@ __device__ inline void handleFixedJoint(const DeviceState &S, int w, int k, int 
 // and inertia are zero).  4 worlds share a warp, so lanes stay busy although one world has
 // only a handful of contacts per level.
 constexpr int kSolveLanes = 8;
-constexpr int kSolveThreads = 128;
-constexpr int kSolveGroups = kSolveThreads / kSolveLanes;
+constexpr int kSolveGroups = 16;
+constexpr int kSolveThreads = kSolveGroups * kSolveLanes;
 
 struct SolveGroupSmem {
     uint32_t cm[kMaxCand];       // compacted contact meta, creation order
     uint8_t cslot[kMaxCand];     // candidate slot of compacted contact k
     uint8_t clvl[kMaxCand];
+    uint8_t order[kMaxCand];     // contact indices sorted by (level, creation order)
+    uint16_t lvlStart[kMaxCand + 2];
     uint8_t blvl[kMaxBodies + 4];
 };
 
@@ -320,6 +322,8 @@ __device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGro
         g.blvl[s] = fixedBody ? 0xFF : 0;
     }
     __syncwarp(gmask);
+    for (int i = lg; i < K + 2; i += kSolveLanes) g.lvlStart[i] = 0;
+    __syncwarp(gmask);
     int maxLvl = 0;
     if (lg == 0) {
         for (int k = 0; k < K; k++) {
@@ -328,12 +332,22 @@ __device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGro
             int l1 = g.blvl[b1], l2 = g.blvl[b2];
             int lv = max(l1 == 0xFF ? 0 : l1, l2 == 0xFF ? 0 : l2);
             g.clvl[k] = (uint8_t)lv;
+            g.lvlStart[lv + 1] += 1;                 // histogram, turned into offsets below
             if (l1 != 0xFF) g.blvl[b1] = (uint8_t)(lv + 1);
             if (l2 != 0xFF) g.blvl[b2] = (uint8_t)(lv + 1);
             maxLvl = max(maxLvl, lv);
         }
+        for (int l = 1; l <= maxLvl + 1; l++) g.lvlStart[l] += g.lvlStart[l - 1];
     }
     maxLvl = __shfl_sync(gmask, maxLvl, gshift);
+    __syncwarp(gmask);
+    // stable counting sort by level: lanes stay dense in every sweep
+    for (int k = lg; k < K; k += kSolveLanes) {
+        const int lv = g.clvl[k];
+        int rank = g.lvlStart[lv];
+        for (int j = 0; j < k; j++) rank += g.clvl[j] == lv;
+        g.order[rank] = (uint8_t)k;
+    }
     __syncwarp(gmask);
     *maxLvlOut = maxLvl;
     return K;
@@ -355,8 +369,9 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve_positions(DeviceState S
     const int K = buildLevels<false>(S, w, g, lg, gmask, gshift, &maxLvl);
     float *contacts = S.contact + size_t(w) * kMaxCand * kContactWords;
     for (int lv = 0; lv <= maxLvl; lv++) {
-        for (int k = lg; k < K; k += kSolveLanes) {
-            if (g.clvl[k] != lv) continue;
+        const int end = K ? g.lvlStart[lv + 1] : 0;
+        for (int i = g.lvlStart[lv] + lg; i < end; i += kSolveLanes) {
+            const int k = g.order[i];
             uint32_t cm = g.cm[k];
             handleContact(S, w, cm, contacts + size_t(g.cslot[k]) * kContactWords,
                           g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
@@ -509,8 +524,9 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve_velocities(DeviceState 
     const int K = buildLevels<true>(S, w, g, lg, gmask, gshift, &maxLvl);
     const float *contacts = S.contact + size_t(w) * kMaxCand * kContactWords;
     for (int lv = 0; lv <= maxLvl; lv++) {
-        for (int k = lg; k < K; k += kSolveLanes) {
-            if (g.clvl[k] != lv) continue;
+        const int end = K ? g.lvlStart[lv + 1] : 0;
+        for (int i = g.lvlStart[lv] + lg; i < end; i += kSolveLanes) {
+            const int k = g.order[i];
             uint32_t cm = g.cm[k];
             solveContactVelocity(S, w, cm, contacts + size_t(g.cslot[k]) * kContactWords,
                                  g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
