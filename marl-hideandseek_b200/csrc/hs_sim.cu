@@ -45,6 +45,12 @@ struct hs_sim {
     int lastLaunches = 0;
     cudaGraphExec_t stepGraph = nullptr;
     cudaStream_t graphStream = nullptr;
+    // The step graph runs the shard as `slices` independent world ranges on parallel branches:
+    // the stage kernels are latency-bound and leave the SMs partly idle (tails of short waves,
+    // low occupancy of the ordered solver), so branches of different slices fill each other's gaps.
+    int slices = 1, branches = 1;
+    cudaStream_t sliceStream[8] = {};
+    cudaEvent_t forkEvent = nullptr, joinEvent[8] = {};
     bool inited = false;
     float cosThreshold = 0.f;
 };
@@ -87,7 +93,7 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     DeviceState &S = sim->S;
     const size_t N = (size_t)cfg->num_worlds;
     RandKey ik = initKey(cfg->rand_seed);
-    S.p = SimParams{cfg->num_worlds, cfg->world_base, A, cfg->sim_flags, ik.a, ik.b,
+    S.p = SimParams{cfg->num_worlds, cfg->num_worlds, cfg->world_base, A, cfg->sim_flags, ik.a, ik.b,
                     cfg->min_hiders, cfg->max_hiders, cfg->min_seekers, cfg->max_seekers};
 
     HS_TRY(devAlloc(sim, &S.body, size_t(BF_COUNT) * kMaxBodies * N));
@@ -145,6 +151,25 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     }
     HS_CUDA(cudaStreamCreateWithFlags(&sim->graphStream, cudaStreamNonBlocking));
     {
+        int want = 2;
+        if (const char *e = getenv("HIDESEEK_STEP_SLICES")) want = atoi(e);
+        if (want < 1) want = 1;
+        if (want > 64) want = 64;
+        while (want > 1 && cfg->num_worlds / want < 512) want--;     // keep slices worth a launch
+        sim->slices = want;
+        int br = 2;
+        if (const char *e = getenv("HIDESEEK_STEP_BRANCHES")) br = atoi(e);
+        if (br < 1) br = 1;
+        if (br > 8) br = 8;
+        if (br > want) br = want;
+        sim->branches = br;
+        HS_CUDA(cudaEventCreateWithFlags(&sim->forkEvent, cudaEventDisableTiming));
+        for (int b = 1; b < br; b++) {
+            HS_CUDA(cudaStreamCreateWithFlags(&sim->sliceStream[b], cudaStreamNonBlocking));
+            HS_CUDA(cudaEventCreateWithFlags(&sim->joinEvent[b], cudaEventDisableTiming));
+        }
+    }
+    {
         // cosf(toRadians(135.f / 2.f)) as the reference's compiler folds it (src/sim.cpp:582,767)
         float mult = 3.14159265358979323846f / 180.f;
         float ang = mult * (135.f / 2.f);
@@ -161,6 +186,11 @@ extern "C" void hs_destroy(hs_sim *sim)
     cudaDeviceSynchronize();
     if (sim->stepGraph) cudaGraphExecDestroy(sim->stepGraph);
     if (sim->graphStream) cudaStreamDestroy(sim->graphStream);
+    if (sim->forkEvent) cudaEventDestroy(sim->forkEvent);
+    for (int b = 1; b < 8; b++) {
+        if (sim->sliceStream[b]) cudaStreamDestroy(sim->sliceStream[b]);
+        if (sim->joinEvent[b]) cudaEventDestroy(sim->joinEvent[b]);
+    }
     for (void *p : sim->allocs) cudaFree(p);
     delete sim;
 }
@@ -278,7 +308,7 @@ extern "C" int hs_last_step_launches(hs_sim *sim) { return sim->lastLaunches; }
 namespace {
 
 struct Launcher {
-    const DeviceState &S;
+    DeviceState S;
     cudaStream_t st;
     int count = 0;
     std::vector<cudaEvent_t> *events = nullptr;     // profiling mode: one event after each launch
@@ -438,8 +468,28 @@ extern "C" int hs_step(hs_sim *sim, void *stream)
         // capture the step once on a private stream; replay on the caller's stream
         cudaGraph_t graph;
         HS_CUDA(cudaStreamBeginCapture(sim->graphStream, cudaStreamCaptureModeThreadLocal));
+        const int N = sim->cfg.num_worlds, B = sim->slices;
+        const int per = ((N + B - 1) / B + 127) / 128 * 128;      // slice starts stay line-aligned
+        int launches = 0;
+        HS_CUDA(cudaEventRecord(sim->forkEvent, sim->graphStream));
+        const int BR = sim->branches;
+        for (int b = 1; b < BR; b++) HS_CUDA(cudaStreamWaitEvent(sim->sliceStream[b], sim->forkEvent, 0));
+        for (int sl = 0; sl < B; sl++) {
+            // slices are dealt round-robin to the branches; a branch runs its slices back to back
+            const int begin = sl * per, count = (begin + per <= N ? per : N - begin);
+            if (count <= 0) continue;
+            const int b = sl % BR;
+            cudaStream_t sb = b == 0 ? sim->graphStream : sim->sliceStream[b];
+            Launcher L{sliceOf(sim->S, begin, count), sb};
+            launchStep(L, sim->cosThreshold);
+            launches += L.count;
+        }
+        for (int b = 1; b < BR; b++) {
+            HS_CUDA(cudaEventRecord(sim->joinEvent[b], sim->sliceStream[b]));
+            HS_CUDA(cudaStreamWaitEvent(sim->graphStream, sim->joinEvent[b], 0));
+        }
         Launcher L{sim->S, sim->graphStream};
-        launchStep(L, sim->cosThreshold);
+        L.count = launches;
         HS_CUDA(cudaStreamEndCapture(sim->graphStream, &graph));
         HS_CUDA(cudaGraphInstantiate(&sim->stepGraph, graph, 0));
         HS_CUDA(cudaGraphDestroy(graph));

@@ -157,7 +157,8 @@ struct AssetTable {
 };
 
 struct SimParams {
-    int numWorlds;           // worlds on this shard
+    int numWorlds;           // worlds this launch covers (the whole shard, or one slice of it)
+    int stride;              // worlds on the shard = SoA row stride of every per-world array
     int worldBase;           // global index of world 0 of this shard (RNG keying)
     int agentsPerWorld;      // A = maxHiders + maxSeekers
     uint32_t simFlags;
@@ -203,30 +204,53 @@ struct DeviceState {
     uint8_t *exCkpt;         // [N,sizeof(Checkpoint)]
 };
 
+// A slice [begin, begin + count) of the shard as its own DeviceState: SoA arrays keep the shard
+// stride and are offset by `begin` worlds, world-major arrays are offset by whole rows.  Worlds
+// never interact, so a step can run as several independent slices (hs_sim.cu: graph branches).
+inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
+{
+    DeviceState V = S;
+    const size_t b = size_t(begin), A = size_t(S.p.agentsPerWorld);
+    V.p.numWorlds = count;
+    V.p.worldBase = S.p.worldBase + begin;
+    V.body += b; V.meta += b; V.wi += b; V.wb += b; V.joint += b; V.jmeta += b;
+    V.bvh += b * kBvhWords;
+    V.cand += b * kMaxCand;
+    V.contact += b * kMaxCand * kContactWords;
+    V.cmeta += b * kMaxCand;
+    V.exReset += b; V.exPrepCounter += b * A; V.exAction += b * A * 5; V.exSelfObs += b * A * 13;
+    V.exSelfType += b * A; V.exSelfMask += b * A; V.exAgentObs += b * A * 5 * 14;
+    V.exBoxObs += b * A * 9 * 17; V.exRampObs += b * A * 2 * 14; V.exAgentVis += b * A * 5;
+    V.exBoxVis += b * A * 9; V.exRampVis += b * A * 2; V.exLidar += b * A * 30; V.exSeed += b * A * 2;
+    V.exReward += b * A; V.exDone += b * A; V.exGlobalPos += b * 17 * 2; V.exPolicy += b * A;
+    V.exEpisodeResult += b * 2; V.exCkptCtrl += b; V.exCkpt += b * kCheckpointBytes;
+    return V;
+}
+
 #if defined(__CUDACC__)
 __device__ __forceinline__ float &BF(const DeviceState &S, int f, int s, int w)
 {
-    return S.body[(size_t(f) * kMaxBodies + s) * S.p.numWorlds + w];
+    return S.body[(size_t(f) * kMaxBodies + s) * S.p.stride + w];
 }
 __device__ __forceinline__ uint32_t &META(const DeviceState &S, int s, int w)
 {
-    return S.meta[size_t(s) * S.p.numWorlds + w];
+    return S.meta[size_t(s) * S.p.stride + w];
 }
 __device__ __forceinline__ int32_t &WI(const DeviceState &S, int f, int w)
 {
-    return S.wi[size_t(f) * S.p.numWorlds + w];
+    return S.wi[size_t(f) * S.p.stride + w];
 }
 __device__ __forceinline__ uint8_t &WB(const DeviceState &S, int f, int w)
 {
-    return S.wb[size_t(f) * S.p.numWorlds + w];
+    return S.wb[size_t(f) * S.p.stride + w];
 }
 __device__ __forceinline__ float &JF(const DeviceState &S, int f, int k, int w)
 {
-    return S.joint[(size_t(f) * kMaxAgents + k) * S.p.numWorlds + w];
+    return S.joint[(size_t(f) * kMaxAgents + k) * S.p.stride + w];
 }
 __device__ __forceinline__ uint32_t &JMETA(const DeviceState &S, int k, int w)
 {
-    return S.jmeta[size_t(k) * S.p.numWorlds + w];
+    return S.jmeta[size_t(k) * S.p.stride + w];
 }
 __device__ __forceinline__ uint32_t *BVH(const DeviceState &S, int w)
 {

@@ -182,7 +182,6 @@ __global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
 
     const uint32_t *blob = BVH(S, w);
     const int nb = WI(S, WF_NUM_BODIES, w);
-    const int N = S.p.numWorlds;
     {
         const int numNodes = min((int)blob[0], kMaxNodes), numLeaves = min((int)blob[1], kMaxBodies);
         const uint4 *src = reinterpret_cast<const uint4 *>(blob);
@@ -191,7 +190,7 @@ __global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
         for (int i = lane; i < nvec; i += 32) dst[i] = src[i];
         for (int l = lane; l < numLeaves; l += 32)
             ws.leafSlot[l] = (uint8_t)(blob[kBvhLeafOff + l * kLeafWords + kLeafInfo] & 0xFF);
-        for (int s = lane; s < nb; s += 32) ws.meta[s] = S.meta[size_t(s) * N + w];
+        for (int s = lane; s < nb; s += 32) ws.meta[s] = META(S, s, w);
     }
     __syncwarp();
 
