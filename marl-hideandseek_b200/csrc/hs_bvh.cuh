@@ -44,14 +44,16 @@ __global__ void k_leaf_update(DeviceState S)
     const int N = S.p.numWorlds;
     long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)kMaxBodies * N) return;
-    int s = int(idx / N), w = int(idx % N);
+    int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
     if (s >= WI(S, WF_NUM_BODIES, w)) return;
 
     uint32_t m = META(S, s, w);
-    Vec3 pos = loadPos(S, s, w);
-    Quat rot = loadRot(S, s, w);
+    const Pose pose = loadPose(S, REC_POSE, s, w);
+    Vec3 pos = pose.x;
+    Quat rot = pose.q;
     Vec3 scale = loadScale(S, s, w);
-    Vec3 vel = loadV3(S, BF_VX, s, w);
+    float4 vel4 = recPtr(S, REC_VEL, s, w)[0];
+    Vec3 vel = {vel4.x, vel4.y, vel4.z};
 
     AABB box = aabbApplyTRS(objAABB(metaObj(m)), pos, rot, scale);
 
@@ -96,7 +98,7 @@ __global__ void k_refit(DeviceState S)
     const int N = S.p.numWorlds;
     long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)kMaxBodies * N) return;
-    int l = int(idx / N), w = int(idx % N);
+    int l = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
     uint32_t *blob = BVH(S, w);
     if (l >= (int)blob[1]) return;
 

@@ -354,7 +354,7 @@ __device__ __forceinline__ void writeContact(const DeviceState &S, int w, int c,
     S.cmeta[size_t(w) * kMaxCand + c] = uint32_t(ref) | (uint32_t(alt) << 8) | (uint32_t(m.n) << 16);
 }
 
-__global__ void __launch_bounds__(kNpThreads) k_narrowphase(DeviceState S)
+__global__ void __launch_bounds__(kNpThreads, 7) k_narrowphase(DeviceState S)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     NpSmem &sm = *reinterpret_cast<NpSmem *>(smemRaw);
@@ -386,8 +386,9 @@ __global__ void __launch_bounds__(kNpThreads) k_narrowphase(DeviceState S)
                 t = objA; objA = objB; objB = t;
                 t = typeA; typeA = typeB; typeB = t;
             }
-            AABB aBox = aabbApplyTRS(objAABBOf(AT, objA), loadPos(S, a, w), loadRot(S, a, w), loadScale(S, a, w));
-            AABB bBox = aabbApplyTRS(objAABBOf(AT, objB), loadPos(S, b, w), loadRot(S, b, w), loadScale(S, b, w));
+            const Pose pa = loadPose(S, REC_POSE, a, w), pb = loadPose(S, REC_POSE, b, w);
+            AABB aBox = aabbApplyTRS(objAABBOf(AT, objA), pa.x, pa.q, loadScale(S, a, w));
+            AABB bBox = aabbApplyTRS(objAABBOf(AT, objB), pb.x, pb.q, loadScale(S, b, w));
             bool plane = typeA == 2 && typeB == 4, hull = typeA == 2 && typeB == 2;
             if (!aabbIntersects(aBox, bBox) || !(plane || hull)) {
                 S.cmeta[size_t(w) * kMaxCand + c] = 0;
@@ -406,9 +407,10 @@ __global__ void __launch_bounds__(kNpThreads) k_narrowphase(DeviceState S)
         const uint32_t rec = sm.list[i];
         const int w = w0 + int(rec & 15), c = int(rec >> 4) & 0xFF, a = int(rec >> 12) & 0xFF, b = int(rec >> 20) & 0xFF;
         WorldHull ha;
-        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], loadPos(S, a, w), loadRot(S, a, w), loadScale(S, a, w));
-        Vec3 n = rotate(loadRot(S, b, w), v3(0, 0, 1));
-        Plane pl = {n, dot(n, loadPos(S, b, w))};
+        const Pose pa = loadPose(S, REC_POSE, a, w), pb = loadPose(S, REC_POSE, b, w);
+        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], pa.x, pa.q, loadScale(S, a, w));
+        Vec3 n = rotate(pb.q, v3(0, 0, 1));
+        Plane pl = {n, dot(n, pb.x)};
         bool has = false;
         Manifold m;
         if (!(hullDistanceFromPlane(pl, ha) > 0.0f)) {
@@ -425,8 +427,9 @@ __global__ void __launch_bounds__(kNpThreads) k_narrowphase(DeviceState S)
         const uint32_t rec = sm.list[kNpListCap - 1 - i];
         const int w = w0 + int(rec & 15), c = int(rec >> 4) & 0xFF, a = int(rec >> 12) & 0xFF, b = int(rec >> 20) & 0xFF;
         WorldHull ha, hb;
-        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], loadPos(S, a, w), loadRot(S, a, w), loadScale(S, a, w));
-        makeWorldHull(hb, AT.hull[metaObj(META(S, b, w))], loadPos(S, b, w), loadRot(S, b, w), loadScale(S, b, w));
+        const Pose pa = loadPose(S, REC_POSE, a, w), pb = loadPose(S, REC_POSE, b, w);
+        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], pa.x, pa.q, loadScale(S, a, w));
+        makeWorldHull(hb, AT.hull[metaObj(META(S, b, w))], pb.x, pb.q, loadScale(S, b, w));
         bool has = false;
         int ref = a, alt = b;
         Manifold m;

@@ -96,7 +96,7 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     S.p = SimParams{cfg->num_worlds, cfg->num_worlds, cfg->world_base, A, cfg->sim_flags, ik.a, ik.b,
                     cfg->min_hiders, cfg->max_hiders, cfg->min_seekers, cfg->max_seekers};
 
-    HS_TRY(devAlloc(sim, &S.body, size_t(BF_COUNT) * kMaxBodies * N));
+    HS_TRY(devAlloc(sim, &S.body, size_t(kBodyWords) * kMaxBodies * N));
     HS_TRY(devAlloc(sim, &S.meta, size_t(kMaxBodies) * N));
     HS_TRY(devAlloc(sim, &S.wi, size_t(WF_COUNT) * N));
     HS_TRY(devAlloc(sim, &S.wb, size_t(WB_COUNT) * N));

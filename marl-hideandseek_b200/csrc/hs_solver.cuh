@@ -25,25 +25,25 @@ __global__ void k_substep(DeviceState S)
     const int N = S.p.numWorlds;
     long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)kMaxBodies * N) return;
-    int s = int(idx / N), w = int(idx % N);
+    int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
     if (s >= WI(S, WF_NUM_BODIES, w)) return;
 
     uint32_t m = META(S, s, w);
-    Vec3 x = loadPos(S, s, w);
-    Quat q = loadRot(S, s, w);
-    storeV3(S, BF_PREV_PX, s, w, x);
-    storeQ(S, BF_PREV_QW, s, w, q);
+    Pose cur = loadPose(S, REC_POSE, s, w);
+    Vec3 x = cur.x;
+    Quat q = cur.q;
+    storePose(S, REC_PREV, s, w, x, q);
 
     if (metaResp(m) == RESP_STATIC) {
-        storeV3(S, BF_PRE_PX, s, w, x);
-        storeQ(S, BF_PRE_QW, s, w, q);
-        storeV3(S, BF_PRE_VX, s, w, {0.f, 0.f, 0.f});
-        storeV3(S, BF_PRE_WX, s, w, {0.f, 0.f, 0.f});
+        storePose(S, REC_PRE, s, w, x, q);
+        storeVel6(S, REC_PREVEL, s, w, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f});
         return;
     }
 
-    Vec3 v = loadV3(S, BF_VX, s, w);
-    Vec3 omega = loadV3(S, BF_WX, s, w);
+    Vel6 vel = loadVel6(S, REC_VEL, s, w);
+    Vel6 ft = loadVel6(S, REC_FORCE, s, w);
+    Vec3 v = vel.v;
+    Vec3 omega = vel.w;
     const ObjectData &O = c_assets.obj[metaObj(m)];
     float inv_m = O.invMass;
     Vec3 inv_I = {O.invInertia[0], O.invInertia[1], O.invInertia[2]};
@@ -53,14 +53,14 @@ __global__ void k_substep(DeviceState S)
         const Vec3 g = -9.8f * v3(0, 0, 1);
         v += h * g;
     }
-    v += (h * inv_m) * loadV3(S, BF_FX, s, w);
+    v += (h * inv_m) * ft.v;
     x += h * v;
 
     Vec3 I = {inv_I.x == 0 ? 0.0f : 1.0f / inv_I.x,
               inv_I.y == 0 ? 0.0f : 1.0f / inv_I.y,
               inv_I.z == 0 ? 0.0f : 1.0f / inv_I.z};
     Quat toLocal = qinv(q);
-    Vec3 tauLocal = rotate(toLocal, loadV3(S, BF_TX, s, w));
+    Vec3 tauLocal = rotate(toLocal, ft.w);
     Vec3 omegaLocal = rotate(toLocal, omega);
     Vec3 IOmega = mulDiag(I, omegaLocal);
     omegaLocal += h * mulDiag(inv_I, tauLocal - cross(omegaLocal, IOmega));
@@ -70,12 +70,9 @@ __global__ void k_substep(DeviceState S)
     q = q + applyOmega * q;
     q = qnormalize(q);
 
-    storeV3(S, BF_PX, s, w, x);
-    storeQ(S, BF_QW, s, w, q);
-    storeV3(S, BF_PRE_PX, s, w, x);
-    storeQ(S, BF_PRE_QW, s, w, q);
-    storeV3(S, BF_PRE_VX, s, w, v);
-    storeV3(S, BF_PRE_WX, s, w, omega);
+    storePose(S, REC_POSE, s, w, x, q);
+    storePose(S, REC_PRE, s, w, x, q);
+    storeVel6(S, REC_PREVEL, s, w, v, omega);
 }
 
 struct MassData { float inv_m; Vec3 inv_I; float muS, muD; };
@@ -177,12 +174,13 @@ __device__ inline void handleContact(const DeviceState &S, int w, uint32_t meta,
     Vec3 avg; float pen;
     if (avgContact(c, &avg, &pen)) return;
 
-    Vec3 x1 = loadPos(S, b1, w), x2 = loadPos(S, b2, w);
-    Quat q1 = loadRot(S, b1, w), q2 = loadRot(S, b2, w);
+    const Pose cur1 = loadPose(S, REC_POSE, b1, w), cur2 = loadPose(S, REC_POSE, b2, w);
+    const Pose pre1 = loadPose(S, REC_PRE, b1, w), pre2 = loadPose(S, REC_PRE, b2, w);
+    const Pose prev1 = loadPose(S, REC_PREV, b1, w), prev2 = loadPose(S, REC_PREV, b2, w);
+    Vec3 x1 = cur1.x, x2 = cur2.x;
+    Quat q1 = cur1.q, q2 = cur2.q;
     Vec3 r1, r2;
-    localContacts(loadV3(S, BF_PRE_PX, b1, w), loadQ(S, BF_PRE_QW, b1, w),
-                  loadV3(S, BF_PRE_PX, b2, w), loadQ(S, BF_PRE_QW, b2, w),
-                  avg, pen, c.normal, &r1, &r2);
+    localContacts(pre1.x, pre1.q, pre2.x, pre2.q, avg, pen, c.normal, &r1, &r2);
 
     // handleContactConstraint
     Vec3 n = c.normal;
@@ -192,8 +190,8 @@ __device__ inline void handleContact(const DeviceState &S, int w, uint32_t meta,
     if (d > 0) {
         lambda_n = applyPositionalFull(x1, x2, q1, q2, r1, r2, m1, m2, n, d, 0.f);
 
-        Vec3 p1_hat = rotate(loadQ(S, BF_PREV_QW, b1, w), r1) + loadV3(S, BF_PREV_PX, b1, w);
-        Vec3 p2_hat = rotate(loadQ(S, BF_PREV_QW, b2, w), r2) + loadV3(S, BF_PREV_PX, b2, w);
+        Vec3 p1_hat = rotate(prev1.q, r1) + prev1.x;
+        Vec3 p2_hat = rotate(prev2.q, r2) + prev2.x;
         p1 = rotate(q1, r1) + x1;
         p2 = rotate(q2, r2) + x2;
         Vec3 dp = (p1 - p1_hat) - (p2 - p2_hat);
@@ -212,15 +210,16 @@ __device__ inline void handleContact(const DeviceState &S, int w, uint32_t meta,
     }
     cdata[19] = lambda_n;
 
-    if (write1) { storeV3(S, BF_PX, b1, w, x1); storeQ(S, BF_QW, b1, w, q1); }
-    if (write2) { storeV3(S, BF_PX, b2, w, x2); storeQ(S, BF_QW, b2, w, q2); }
+    if (write1) storePose(S, REC_POSE, b1, w, x1, q1);
+    if (write2) storePose(S, REC_POSE, b2, w, x2, q2);
 }
 
 __device__ inline void handleFixedJoint(const DeviceState &S, int w, int k, int b1, int b2)
 {
     MassData m1 = massOf(META(S, b1, w)), m2 = massOf(META(S, b2, w));
-    Vec3 x1 = loadPos(S, b1, w), x2 = loadPos(S, b2, w);
-    Quat q1 = loadRot(S, b1, w), q2 = loadRot(S, b2, w);
+    const Pose jp1 = loadPose(S, REC_POSE, b1, w), jp2 = loadPose(S, REC_POSE, b2, w);
+    Vec3 x1 = jp1.x, x2 = jp2.x;
+    Quat q1 = jp1.q, q2 = jp2.q;
     Quat a1 = {JF(S, JF_A1W, k, w), JF(S, JF_A1X, k, w), JF(S, JF_A1Y, k, w), JF(S, JF_A1Z, k, w)};
     Quat a2 = {JF(S, JF_A2W, k, w), JF(S, JF_A2X, k, w), JF(S, JF_A2Y, k, w), JF(S, JF_A2Z, k, w)};
     Vec3 jr1 = {JF(S, JF_R1X, k, w), JF(S, JF_R1Y, k, w), JF(S, JF_R1Z, k, w)};
@@ -263,8 +262,8 @@ __device__ inline void handleFixedJoint(const DeviceState &S, int w, int k, int 
         corr = corr / cmag;
         applyPositionalFull(x1, x2, q1, q2, jr1, jr2, m1, m2, corr, cmag, 0.f);
     }
-    storeV3(S, BF_PX, b1, w, x1); storeV3(S, BF_PX, b2, w, x2);
-    storeQ(S, BF_QW, b1, w, q1); storeQ(S, BF_QW, b2, w, q2);
+    storePose(S, REC_POSE, b1, w, x1, q1);
+    storePose(S, REC_POSE, b2, w, x2, q2);
 }
 
 // ---- ordered Gauss-Seidel without one-thread-per-world serialisation -----------------------------
@@ -316,9 +315,10 @@ __device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGro
     for (int s = lg; s < nb; s += kSolveLanes) {
         uint32_t m = META(S, s, w);
         bool fixedBody = metaResp(m) == RESP_STATIC;
-        if (!kVelocityPass)
-            fixedBody = fixedBody && BF(S, BF_QW, s, w) == 1.f && BF(S, BF_QX, s, w) == 0.f &&
-                        BF(S, BF_QY, s, w) == 0.f && BF(S, BF_QZ, s, w) == 0.f;
+        if (!kVelocityPass && fixedBody) {
+            Quat q = loadRot(S, s, w);
+            fixedBody = q.w == 1.f && q.x == 0.f && q.y == 0.f && q.z == 0.f;
+        }
         g.blvl[s] = fixedBody ? 0xFF : 0;
     }
     __syncwarp(gmask);
@@ -405,18 +405,18 @@ __global__ void k_set_velocities(DeviceState S)
     const int N = S.p.numWorlds;
     long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)kMaxBodies * N) return;
-    int s = int(idx / N), w = int(idx % N);
+    int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
     if (s >= WI(S, WF_NUM_BODIES, w)) return;
 
     const float h = substepH();
-    Vec3 x = loadPos(S, s, w), xp = loadV3(S, BF_PREV_PX, s, w);
-    Quat q = loadRot(S, s, w), qp = loadQ(S, BF_PREV_QW, s, w);
+    const Pose cur = loadPose(S, REC_POSE, s, w), prev = loadPose(S, REC_PREV, s, w);
+    Vec3 x = cur.x, xp = prev.x;
+    Quat q = cur.q, qp = prev.q;
     Quat dq;
     if (q.w != qp.w || q.x != qp.x || q.y != qp.y || q.z != qp.z) dq = q * qinv(qp);
     else dq = {1.f, 0.f, 0.f, 0.f};
     Vec3 newOmega = (2.f / h) * v3(dq.x, dq.y, dq.z);
-    storeV3(S, BF_VX, s, w, (x - xp) / h);
-    storeV3(S, BF_WX, s, w, dq.w > 0.f ? newOmega : -newOmega);
+    storeVel6(S, REC_VEL, s, w, (x - xp) / h, dq.w > 0.f ? newOmega : -newOmega);
 }
 
 __device__ __forceinline__ Vec3 relVel(Vec3 v1, Vec3 v2, Vec3 o1, Vec3 o2, Vec3 d1, Vec3 d2)
@@ -435,11 +435,14 @@ __device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_
     const float gMag = sqrtf(0.f * 0.f + 0.f * 0.f + 9.8f * 9.8f);
     const float restThreshold = 2.f * gMag * h;
 
-    Vec3 v1 = loadV3(S, BF_VX, b1, w), o1 = loadV3(S, BF_WX, b1, w);
-    Vec3 v2 = loadV3(S, BF_VX, b2, w), o2 = loadV3(S, BF_WX, b2, w);
+    const Vel6 vel1 = loadVel6(S, REC_VEL, b1, w), vel2 = loadVel6(S, REC_VEL, b2, w);
+    const Vel6 pv1 = loadVel6(S, REC_PREVEL, b1, w), pv2 = loadVel6(S, REC_PREVEL, b2, w);
+    const Pose pre1 = loadPose(S, REC_PRE, b1, w), pre2 = loadPose(S, REC_PRE, b2, w);
+    Vec3 v1 = vel1.v, o1 = vel1.w;
+    Vec3 v2 = vel2.v, o2 = vel2.w;
     Quat q1 = loadRot(S, b1, w), q2 = loadRot(S, b2, w);
-    Vec3 px1 = loadV3(S, BF_PRE_PX, b1, w), px2 = loadV3(S, BF_PRE_PX, b2, w);
-    Quat pq1 = loadQ(S, BF_PRE_QW, b1, w), pq2 = loadQ(S, BF_PRE_QW, b2, w);
+    Vec3 px1 = pre1.x, px2 = pre2.x;
+    Quat pq1 = pre1.q, pq2 = pre2.q;
     float muD = 0.5f * (m1.muD + m2.muD);
     Vec3 n = c.normal;
 
@@ -449,8 +452,7 @@ __device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_
         Vec3 r1, r2;
         localContacts(px1, pq1, px2, pq2, avg, pen, n, &r1, &r2);
         Vec3 r1pre = rotate(pq1, r1), r2pre = rotate(pq2, r2);
-        Vec3 vbar = relVel(loadV3(S, BF_PRE_VX, b1, w), loadV3(S, BF_PRE_VX, b2, w),
-                           loadV3(S, BF_PRE_WX, b1, w), loadV3(S, BF_PRE_WX, b2, w), r1pre, r2pre);
+        Vec3 vbar = relVel(pv1.v, pv2.v, pv1.w, pv2.w, r1pre, r2pre);
         float vnBar = dot(n, vbar);
         Vec3 r1w = rotate(q1, r1), r2w = rotate(q2, r2);
         Vec3 ta1 = cross(r1, rotate(qinv(q1), n)), ta2 = cross(r2, rotate(qinv(q2), n));
@@ -504,8 +506,8 @@ __device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_
         o2 -= rotate(q2, imp * fr2);
     }
 
-    if (write1) { storeV3(S, BF_VX, b1, w, v1); storeV3(S, BF_WX, b1, w, o1); }
-    if (write2) { storeV3(S, BF_VX, b2, w, v2); storeV3(S, BF_WX, b2, w, o2); }
+    if (write1) storeVel6(S, REC_VEL, b1, w, v1, o1);
+    if (write2) storeVel6(S, REC_VEL, b2, w, v2, o2);
 }
 
 // solveVelocities

@@ -63,6 +63,20 @@ enum BodyField : int {
     BF_COUNT
 };
 
+// ---- body records -------------------------------------------------------------------------------
+// In HBM a body is seven 32-byte records, world-major: body[world][slot][record][8 floats]
+//   R0 pose (pos3, quat4)   R1 scale3        R2 velocity (lin3, ang3)   R3 force3, torque3
+//   R4 previous pose        R5 pre-solve pose                         R6 pre-solve velocity
+// One record = one 32-byte sector = two 128-bit accesses, so the pair-centric stages
+// (narrowphase, ordered solver, rays) move whole sectors of useful bytes per body instead of
+// one 4-byte lane of seven different sectors, and the 224 bytes of a body — hence the ~6 KB of
+// a world — are contiguous for the body-parallel stages.  BodyField indices address components
+// through recOf / compOf, so scalar code is layout-agnostic.
+constexpr int kRecWords = 8, kBodyRecs = 7, kBodyWords = kRecWords * kBodyRecs;
+enum BodyRec : int { REC_POSE = 0, REC_SCALE, REC_VEL, REC_FORCE, REC_PREV, REC_PRE, REC_PREVEL };
+HS_HD constexpr int recOf(int f) { return f < BF_SX ? 0 : f < BF_VX ? 1 : f < BF_FX ? 2 : f < BF_PREV_PX ? 3 : f < BF_PRE_PX ? 4 : f < BF_PRE_VX ? 5 : 6; }
+HS_HD constexpr int compOf(int f) { return f < BF_SX ? f : f < BF_VX ? f - BF_SX : f < BF_FX ? f - BF_VX : f < BF_PREV_PX ? f - BF_FX : f < BF_PRE_PX ? f - BF_PREV_PX : f < BF_PRE_VX ? f - BF_PRE_PX : f - BF_PRE_VX; }
+
 // body meta word: obj | resp<<4 | owner<<6 | entity_id<<8 | leaf<<16
 HS_HD uint32_t packMeta(int obj, int resp, int owner, int eid, int leaf)
 {
@@ -168,8 +182,8 @@ struct SimParams {
 
 struct DeviceState {
     SimParams p;
-    float *body;             // [BF_COUNT][kMaxBodies][N]
-    uint32_t *meta;          // [kMaxBodies][N]
+    float *body;             // [N][kMaxBodies][kBodyRecs][8]
+    uint32_t *meta;          // [N][kMaxBodies]
     int32_t *wi;             // [WF_COUNT][N]
     uint8_t *wb;             // [WB_COUNT][N]
     float *joint;            // [JF_COUNT][kMaxAgents][N]
@@ -213,7 +227,7 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
     const size_t b = size_t(begin), A = size_t(S.p.agentsPerWorld);
     V.p.numWorlds = count;
     V.p.worldBase = S.p.worldBase + begin;
-    V.body += b; V.meta += b; V.wi += b; V.wb += b; V.joint += b; V.jmeta += b;
+    V.body += b * kMaxBodies * kBodyWords; V.meta += b * kMaxBodies; V.wi += b; V.wb += b; V.joint += b; V.jmeta += b;
     V.bvh += b * kBvhWords;
     V.cand += b * kMaxCand;
     V.contact += b * kMaxCand * kContactWords;
@@ -230,11 +244,11 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
 #if defined(__CUDACC__)
 __device__ __forceinline__ float &BF(const DeviceState &S, int f, int s, int w)
 {
-    return S.body[(size_t(f) * kMaxBodies + s) * S.p.stride + w];
+    return S.body[((size_t(w) * kMaxBodies + s) * kBodyRecs + recOf(f)) * kRecWords + compOf(f)];
 }
 __device__ __forceinline__ uint32_t &META(const DeviceState &S, int s, int w)
 {
-    return S.meta[size_t(s) * S.p.stride + w];
+    return S.meta[size_t(w) * kMaxBodies + s];
 }
 __device__ __forceinline__ int32_t &WI(const DeviceState &S, int f, int w)
 {
@@ -257,17 +271,53 @@ __device__ __forceinline__ uint32_t *BVH(const DeviceState &S, int w)
     return S.bvh + size_t(w) * kBvhWords;
 }
 
+// ---- record-granular (128-bit) access --------------------------------------------------------------
+__device__ __forceinline__ float4 *recPtr(const DeviceState &S, int rec, int s, int w)
+{
+    return reinterpret_cast<float4 *>(S.body + ((size_t(w) * kMaxBodies + s) * kBodyRecs + rec) * kRecWords);
+}
+struct Pose { Vec3 x; Quat q; };
+struct Vel6 { Vec3 v; Vec3 w; };
+// pose-shaped records: REC_POSE, REC_PREV, REC_PRE
+__device__ __forceinline__ Pose loadPose(const DeviceState &S, int rec, int s, int w)
+{
+    const float4 *p = recPtr(S, rec, s, w);
+    float4 a = p[0], b = p[1];
+    return {{a.x, a.y, a.z}, {a.w, b.x, b.y, b.z}};
+}
+__device__ __forceinline__ void storePose(const DeviceState &S, int rec, int s, int w, Vec3 x, Quat q)
+{
+    float4 *p = recPtr(S, rec, s, w);
+    p[0] = make_float4(x.x, x.y, x.z, q.w);
+    p[1] = make_float4(q.x, q.y, q.z, 0.f);
+}
+// six-vector records: REC_VEL (linear, angular), REC_FORCE (force, torque), REC_PREVEL
+__device__ __forceinline__ Vel6 loadVel6(const DeviceState &S, int rec, int s, int w)
+{
+    const float4 *p = recPtr(S, rec, s, w);
+    float4 a = p[0], b = p[1];
+    return {{a.x, a.y, a.z}, {a.w, b.x, b.y}};
+}
+__device__ __forceinline__ void storeVel6(const DeviceState &S, int rec, int s, int w, Vec3 v, Vec3 o)
+{
+    float4 *p = recPtr(S, rec, s, w);
+    p[0] = make_float4(v.x, v.y, v.z, o.x);
+    p[1] = make_float4(o.y, o.z, 0.f, 0.f);
+}
+
 __device__ __forceinline__ Vec3 loadPos(const DeviceState &S, int s, int w)
 {
-    return {BF(S, BF_PX, s, w), BF(S, BF_PY, s, w), BF(S, BF_PZ, s, w)};
+    float4 a = recPtr(S, REC_POSE, s, w)[0];
+    return {a.x, a.y, a.z};
 }
 __device__ __forceinline__ Quat loadRot(const DeviceState &S, int s, int w)
 {
-    return {BF(S, BF_QW, s, w), BF(S, BF_QX, s, w), BF(S, BF_QY, s, w), BF(S, BF_QZ, s, w)};
+    return loadPose(S, REC_POSE, s, w).q;
 }
 __device__ __forceinline__ Vec3 loadScale(const DeviceState &S, int s, int w)
 {
-    return {BF(S, BF_SX, s, w), BF(S, BF_SY, s, w), BF(S, BF_SZ, s, w)};
+    float4 a = recPtr(S, REC_SCALE, s, w)[0];
+    return {a.x, a.y, a.z};
 }
 __device__ __forceinline__ Vec3 loadV3(const DeviceState &S, int f0, int s, int w)
 {
