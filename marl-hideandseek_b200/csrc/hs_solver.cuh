@@ -125,17 +125,24 @@ struct ContactView {
     float depth[4];
     int n;
     Vec3 normal;
+    float lambdaN;
 };
 
 __device__ __forceinline__ ContactView loadContact(const float *c, uint32_t meta)
 {
+    // contact rows are 80 bytes, 16-byte aligned (hs_narrowphase.cuh::writeContact)
+    const float4 *c4 = reinterpret_cast<const float4 *>(c);
     ContactView v;
+#pragma unroll
     for (int i = 0; i < 4; i++) {
-        v.pts[i] = {c[i * 4], c[i * 4 + 1], c[i * 4 + 2]};
-        v.depth[i] = c[i * 4 + 3];
+        float4 p = c4[i];
+        v.pts[i] = {p.x, p.y, p.z};
+        v.depth[i] = p.w;
     }
+    float4 n = c4[4];
     v.n = int(meta >> 16) & 0xFF;
-    v.normal = {c[16], c[17], c[18]};
+    v.normal = {n.x, n.y, n.z};
+    v.lambdaN = n.w;
     return v;
 }
 
@@ -279,15 +286,15 @@ __device__ inline void handleFixedJoint(const DeviceState &S, int w, int k, int 
 // and inertia are zero).  4 worlds share a warp, so lanes stay busy although one world has
 // only a handful of contacts per level.
 constexpr int kSolveLanes = 8;
+constexpr int kMaxLevels = 126;    // deeper dependency chains fall back to the serial order
 constexpr int kSolveGroups = 16;
 constexpr int kSolveThreads = kSolveGroups * kSolveLanes;
 
 struct SolveGroupSmem {
-    uint32_t cm[kMaxCand];       // compacted contact meta, creation order
-    uint8_t cslot[kMaxCand];     // candidate slot of compacted contact k
+    uint32_t cm[kMaxCand];       // compacted contact meta (creation order) | candidate slot << 24
     uint8_t clvl[kMaxCand];
     uint8_t order[kMaxCand];     // contact indices sorted by (level, creation order)
-    uint16_t lvlStart[kMaxCand + 2];
+    uint16_t lvlStart[kMaxLevels + 2];
     uint8_t blvl[kMaxBodies + 4];
 };
 
@@ -307,8 +314,7 @@ __device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGro
         const unsigned bal = (__ballot_sync(gmask, has) >> gshift) & ((1u << kSolveLanes) - 1u);
         if (has) {
             int k = K + __popc(bal & ((1u << lg) - 1u));
-            g.cm[k] = m;
-            g.cslot[k] = (uint8_t)c;
+            g.cm[k] = (m & 0x00FFFFFFu) | (uint32_t(c) << 24);
         }
         K += __popc(bal);
     }
@@ -322,7 +328,7 @@ __device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGro
         g.blvl[s] = fixedBody ? 0xFF : 0;
     }
     __syncwarp(gmask);
-    for (int i = lg; i < K + 2; i += kSolveLanes) g.lvlStart[i] = 0;
+    for (int i = lg; i < kMaxLevels + 2; i += kSolveLanes) g.lvlStart[i] = 0;
     __syncwarp(gmask);
     int maxLvl = 0;
     if (lg == 0) {
@@ -330,17 +336,22 @@ __device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGro
             uint32_t cm = g.cm[k];
             int b1 = cm & 0xFF, b2 = (cm >> 8) & 0xFF;
             int l1 = g.blvl[b1], l2 = g.blvl[b2];
-            int lv = max(l1 == 0xFF ? 0 : l1, l2 == 0xFF ? 0 : l2);
+            int lv = min(max(l1 == 0xFF ? 0 : l1, l2 == 0xFF ? 0 : l2), 0xFE);
             g.clvl[k] = (uint8_t)lv;
-            g.lvlStart[lv + 1] += 1;                 // histogram, turned into offsets below
+            if (lv < kMaxLevels) g.lvlStart[lv + 1] += 1;      // histogram, turned into offsets below
             if (l1 != 0xFF) g.blvl[b1] = (uint8_t)(lv + 1);
             if (l2 != 0xFF) g.blvl[b2] = (uint8_t)(lv + 1);
             maxLvl = max(maxLvl, lv);
         }
-        for (int l = 1; l <= maxLvl + 1; l++) g.lvlStart[l] += g.lvlStart[l - 1];
+        if (maxLvl < kMaxLevels)
+            for (int l = 1; l <= maxLvl + 1; l++) g.lvlStart[l] += g.lvlStart[l - 1];
     }
     maxLvl = __shfl_sync(gmask, maxLvl, gshift);
     __syncwarp(gmask);
+    if (maxLvl >= kMaxLevels) {        // pathological chain: signal the serial fallback
+        *maxLvlOut = -1;
+        return K;
+    }
     // stable counting sort by level: lanes stay dense in every sweep
     for (int k = lg; k < K; k += kSolveLanes) {
         const int lv = g.clvl[k];
@@ -373,11 +384,14 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve_positions(DeviceState S
         for (int i = g.lvlStart[lv] + lg; i < end; i += kSolveLanes) {
             const int k = g.order[i];
             uint32_t cm = g.cm[k];
-            handleContact(S, w, cm, contacts + size_t(g.cslot[k]) * kContactWords,
+            handleContact(S, w, cm, contacts + size_t(cm >> 24) * kContactWords,
                           g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
         }
         __syncwarp(gmask);
     }
+    if (maxLvl < 0 && lg == 0)
+        for (int k = 0; k < K; k++) handleContact(S, w, g.cm[k], contacts + size_t(g.cm[k] >> 24) * kContactWords, true, true);
+    __syncwarp(gmask);
 
     // joints in creation order (at most one Fixed joint per agent; rare)
     if (lg == 0) {
@@ -429,7 +443,7 @@ __device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_
 {
     const int b1 = meta & 0xFF, b2 = (meta >> 8) & 0xFF;
     ContactView c = loadContact(cdata, meta);
-    const float lambdaN = cdata[19];
+    const float lambdaN = c.lambdaN;
     MassData m1 = massOf(META(S, b1, w)), m2 = massOf(META(S, b2, w));
     const float h = substepH();
     const float gMag = sqrtf(0.f * 0.f + 0.f * 0.f + 9.8f * 9.8f);
@@ -530,11 +544,13 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve_velocities(DeviceState 
         for (int i = g.lvlStart[lv] + lg; i < end; i += kSolveLanes) {
             const int k = g.order[i];
             uint32_t cm = g.cm[k];
-            solveContactVelocity(S, w, cm, contacts + size_t(g.cslot[k]) * kContactWords,
+            solveContactVelocity(S, w, cm, contacts + size_t(cm >> 24) * kContactWords,
                                  g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
         }
         __syncwarp(gmask);
     }
+    if (maxLvl < 0 && lg == 0)
+        for (int k = 0; k < K; k++) solveContactVelocity(S, w, g.cm[k], contacts + size_t(g.cm[k] >> 24) * kContactWords, true, true);
     if (lg == 0) WI(S, WF_NUM_CONTACTS, w) = K;
 }
 
