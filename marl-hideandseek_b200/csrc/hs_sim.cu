@@ -48,6 +48,7 @@ struct hs_sim {
     // The step graph runs the shard as `slices` independent world ranges on parallel branches:
     // the stage kernels are latency-bound and leave the SMs partly idle (tails of short waves,
     // low occupancy of the ordered solver), so branches of different slices fill each other's gaps.
+    bool raysNearestFirst = true;
     int slices = 1, branches = 1;
     cudaStream_t sliceStream[8] = {};
     cudaEvent_t forkEvent = nullptr, joinEvent[8] = {};
@@ -147,7 +148,9 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
             dirs[i][0] = cs; dirs[i][1] = sn;
         }
         HS_CUDA(cudaMemcpyToSymbol(c_lidarDir, dirs, sizeof(dirs)));
-        HS_CUDA(cudaFuncSetAttribute(k_rays, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
+        HS_CUDA(cudaFuncSetAttribute(k_rays<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
+        HS_CUDA(cudaFuncSetAttribute(k_rays<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
+        if (const char *e = getenv("HIDESEEK_RAY_ORDER")) sim->raysNearestFirst = strcmp(e, "reference") != 0;
     }
     HS_CUDA(cudaStreamCreateWithFlags(&sim->graphStream, cudaStreamNonBlocking));
     {
@@ -346,15 +349,17 @@ void launchBroadphaseSetup(Launcher &L, bool mayRebuild)
 }
 
 // observationsTasks (src/sim.cpp:1232-1293)
-void launchObservations(Launcher &L, float cosThr)
+void launchObservations(Launcher &L, float cosThr, bool nearestFirst)
 {
     k_observations<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.mark("k_observations");
-    k_rays<<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr); L.mark("k_rays");
+    if (nearestFirst) k_rays<true><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
+    else k_rays<false><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
+    L.mark("k_rays");
     k_debug_positions<<<L.gWorld(), 128, 0, L.st>>>(L.S); L.mark("k_debug_positions");
 }
 
 // Step task graph (src/sim.cpp:1307-1313), node order of SURVEY.md §3.3
-void launchStep(Launcher &L, float cosThr)
+void launchStep(Launcher &L, float cosThr, bool nearestFirst)
 {
     k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.mark("k_move");
     launchBroadphaseSetup(L, true);
@@ -372,10 +377,12 @@ void launchStep(Launcher &L, float cosThr)
     if (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) {
         k_zero_agent_vel<<<dim3((L.N() * kMaxAgents + 127) / 128), 128, 0, L.st>>>(L.S); L.mark("k_zero_agent_vel");
     }
-    k_rewards<<<(L.N() + kRewardWarps - 1) / kRewardWarps, kRewardWarps * 32, 0, L.st>>>(L.S, cosThr); L.mark("k_rewards");
+    if (nearestFirst) k_rewards<true><<<(L.N() + kRewardWarps - 1) / kRewardWarps, kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
+    else k_rewards<false><<<(L.N() + kRewardWarps - 1) / kRewardWarps, kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
+    L.mark("k_rewards");
     k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_reset");
     launchBroadphaseSetup(L, true);
-    launchObservations(L, cosThr);
+    launchObservations(L, cosThr, nearestFirst);
 }
 
 }  // namespace
@@ -389,7 +396,7 @@ extern "C" int hs_init(hs_sim *sim, void *stream)
     // Init task graph (src/sim.cpp:1295-1305): reset -> broadphase setup -> observations
     k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S);
     launchBroadphaseSetup(L, true);
-    launchObservations(L, sim->cosThreshold);
+    launchObservations(L, sim->cosThreshold, sim->raysNearestFirst);
     HS_CUDA(cudaGetLastError());
     sim->inited = true;
     return 0;
@@ -481,7 +488,7 @@ extern "C" int hs_step(hs_sim *sim, void *stream)
             const int b = sl % BR;
             cudaStream_t sb = b == 0 ? sim->graphStream : sim->sliceStream[b];
             Launcher L{sliceOf(sim->S, begin, count), sb};
-            launchStep(L, sim->cosThreshold);
+            launchStep(L, sim->cosThreshold, sim->raysNearestFirst);
             launches += L.count;
         }
         for (int b = 1; b < BR; b++) {
@@ -517,7 +524,7 @@ extern "C" int hs_load_checkpoints(hs_sim *sim, void *stream)
     Launcher L{sim->S, (cudaStream_t)stream};
     k_load_checkpoint<<<L.gWorld(64), 64, 0, L.st>>>(L.S);
     launchBroadphaseSetup(L, true);            // postGenTasks
-    launchObservations(L, sim->cosThreshold);  // observationsTasks
+    launchObservations(L, sim->cosThreshold, sim->raysNearestFirst);  // observationsTasks
     HS_CUDA(cudaGetLastError());
     return 0;
 }
@@ -584,7 +591,7 @@ extern "C" int hs_step_profiled(hs_sim *sim, void *stream, float *ms_out, int ca
     Launcher L{sim->S, st};
     L.events = &ev;
     L.names = &g_profNames;
-    launchStep(L, sim->cosThreshold);
+    launchStep(L, sim->cosThreshold, sim->raysNearestFirst);
     HS_CUDA(cudaStreamSynchronize(st));
     cudaEvent_t prev = start;
     int n = 0;
