@@ -181,74 +181,68 @@ __device__ inline int traceRayWarp(const uint32_t *blob, const AssetTable &AT, b
     return int(blob[kBvhLeafOff + hitLeaf * kLeafWords + kLeafInfo] & 0xFF);
 }
 
-// Front-to-back variant: hit children (leaves and inner nodes alike) are pushed far-to-near with
-// their slab entry distance, so the nearest is popped first and everything whose entry lies
-// beyond the current closest hit is discarded at pop time.  The closest hit is a property of the
-// ray and the leaves, not of the visiting order; the only order-dependent case is an exact
-// floating-point tie between two different leaves (the reference keeps the later-visited one),
-// which changes neither a lidar depth nor — short of two bodies sharing their entry face at the
-// hit point — a visibility bit.
-__device__ inline int traceRayWarpOrdered(const uint32_t *blob, const AssetTable &AT, bool active,
-                                          Vec3 o, Vec3 d, float t_max, float *out_t)
+// Default closest-hit query: no hierarchy walk at all.  A world has at most 52 leaves (~29 live),
+// so every lane slab-tests ALL leaf boxes in one uniform loop — the whole warp reads the same
+// leaf record (a shared-memory broadcast) and no lane diverges — remembering the set of boxes
+// its ray enters (one 64-bit mask) and the nearest of them.  The nearest box is tested first
+// (all lanes together); the few remaining candidates are re-checked against the now short
+// t_max and tested with the same parked-lane vote as the reference-order walk.
+// The closest hit is a property of the ray and the leaves, not of the visiting order or of the
+// hierarchy; the only order-dependent case is an exact floating-point tie between two different
+// leaves, which changes neither a lidar depth nor — short of two bodies sharing their entry face
+// at the hit point — a visibility bit (tests/test_ray_order_gpu.py compares both modes bit-wise).
+__device__ inline int traceRayFlat(const uint32_t *blob, const AssetTable &AT, bool active,
+                                   Vec3 o, Vec3 d, float t_max, float *out_t)
 {
     const Vec3 inv = {1.f / d.x, 1.f / d.y, 1.f / d.z};
-    int32_t stackC[24];
-    float stackA[24];
-    int sp = 0;
-    int pending = -1;
+    const int numLeaves = min((int)blob[1], kMaxBodies);
+    unsigned long long mask = 0ull;
+    float bestA = INFINITY;
+    int bestL = -1;
+#define HS_LEAF_SLAB(L, A, OK)                                                                 \
+    {                                                                                          \
+        float tlx = inv.x * (L[0] - o.x), tly = inv.y * (L[1] - o.y), tlz = inv.z * (L[2] - o.z); \
+        float tux = inv.x * (L[3] - o.x), tuy = inv.y * (L[4] - o.y), tuz = inv.z * (L[5] - o.z); \
+        float mnx = fminf(tlx, tux), mny = fminf(tly, tuy), mnz = fminf(tlz, tuz);            \
+        float mxx = fmaxf(tlx, tux), mxy = fmaxf(tly, tuy), mxz = fmaxf(tlz, tuz);            \
+        A = fmaxf(mnx, fmaxf(mny, fmaxf(mnz, 0.f)));                                           \
+        OK = A <= fminf(mxx, fminf(mxy, fminf(mxz, t_max)));                                   \
+    }
+    for (int l = 0; l < numLeaves; l++) {
+        const float *L = leafF(blob, l);
+        float a;
+        bool ok;
+        HS_LEAF_SLAB(L, a, ok)
+        if (ok && active) {
+            mask |= 1ull << l;
+            if (a < bestA) { bestA = a; bestL = l; }
+        }
+    }
     int hitLeaf = -1;
-    bool done = !active;
-    if (active) { stackC[0] = 0; stackA[0] = 0.f; sp = 1; }
-
+    if (bestL >= 0) {
+        float t;
+        if (traceLeafS(blob, AT, bestL, o, d, t_max, &t)) { t_max = t; hitLeaf = bestL; }
+        mask &= ~(1ull << bestL);
+    }
+    int pending = -1;
+    bool done = mask == 0ull;
     while (true) {
         if (!done && pending < 0) {
-            // pop until something survives the current t_max
-            int cur = kSentinel;
-            while (sp > 0) {
-                --sp;
-                if (stackA[sp] <= t_max) { cur = stackC[sp]; break; }
+            while (mask) {
+                const int l = __ffsll((long long)mask) - 1;
+                mask &= mask - 1ull;
+                const float *L = leafF(blob, l);
+                float a;
+                bool ok;
+                HS_LEAF_SLAB(L, a, ok)
+                if (ok) { pending = l; break; }
             }
-            if (cur == kSentinel) {
-                done = true;
-            } else if (cur < 0) {
-                pending = cur & 0x7FFFFFFF;
-            } else {
-                const float4 *nf = reinterpret_cast<const float4 *>(blob + kBvhNodeOff + cur * kNodeWords);
-                const float4 lox = nf[0], loy = nf[1], loz = nf[2], hix = nf[3], hiy = nf[4], hiz = nf[5];
-                const int4 ch = *reinterpret_cast<const int4 *>(blob + kBvhNodeOff + cur * kNodeWords + kNodeChild);
-                float a0, a1, a2, a3;
-                int c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
-#define HS_SLAB(LX, LY, LZ, HX, HY, HZ, A, C)                                                  \
-                {                                                                              \
-                    float tlx = inv.x * (LX - o.x), tly = inv.y * (LY - o.y), tlz = inv.z * (LZ - o.z); \
-                    float tux = inv.x * (HX - o.x), tuy = inv.y * (HY - o.y), tuz = inv.z * (HZ - o.z); \
-                    float mnx = fminf(tlx, tux), mny = fminf(tly, tuy), mnz = fminf(tlz, tuz);        \
-                    float mxx = fmaxf(tlx, tux), mxy = fmaxf(tly, tuy), mxz = fmaxf(tlz, tuz);        \
-                    A = fmaxf(mnx, fmaxf(mny, fmaxf(mnz, 0.f)));                               \
-                    float b = fminf(mxx, fminf(mxy, fminf(mxz, t_max)));                       \
-                    if (C == kSentinel || !(A <= b)) A = INFINITY;                             \
-                }
-                HS_SLAB(lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, a0, c0)
-                HS_SLAB(lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, a1, c1)
-                HS_SLAB(lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, a2, c2)
-                HS_SLAB(lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, a3, c3)
-#undef HS_SLAB
-                // sorting network, descending entry distance (misses = +inf sort first and are skipped)
-#define HS_CSWAP(AA, CA, AB, CB) if (AA < AB) { float ta = AA; AA = AB; AB = ta; int tc = CA; CA = CB; CB = tc; }
-                HS_CSWAP(a0, c0, a1, c1) HS_CSWAP(a2, c2, a3, c3)
-                HS_CSWAP(a0, c0, a2, c2) HS_CSWAP(a1, c1, a3, c3)
-                HS_CSWAP(a1, c1, a2, c2)
-#undef HS_CSWAP
-                if (a0 != INFINITY && sp < 24) { stackC[sp] = c0; stackA[sp++] = a0; }
-                if (a1 != INFINITY && sp < 24) { stackC[sp] = c1; stackA[sp++] = a1; }
-                if (a2 != INFINITY && sp < 24) { stackC[sp] = c2; stackA[sp++] = a2; }
-                if (a3 != INFINITY && sp < 24) { stackC[sp] = c3; stackA[sp++] = a3; }
-            }
+            if (pending < 0) done = true;
         }
         const unsigned act = __ballot_sync(0xFFFFFFFFu, !done);
         if (act == 0) break;
         const unsigned pend = __ballot_sync(0xFFFFFFFFu, pending >= 0);
-        if (pend != 0 && (pend == act || __popc(pend) * HS_VOTE_DEN >= __popc(act) * HS_VOTE_NUM)) {
+        if (pend == act) {
             if (pending >= 0) {
                 float t;
                 if (traceLeafS(blob, AT, pending, o, d, t_max, &t)) { t_max = t; hitLeaf = pending; }
@@ -256,18 +250,19 @@ __device__ inline int traceRayWarpOrdered(const uint32_t *blob, const AssetTable
             }
         }
     }
+#undef HS_LEAF_SLAB
     if (hitLeaf < 0) return -1;
     *out_t = t_max;
     return int(blob[kBvhLeafOff + hitLeaf * kLeafWords + kLeafInfo] & 0xFF);
 }
 
-// kNearestFirst = false keeps the reference's visiting order (ties resolved identically);
-// true is the default (hs_sim.cu: HIDESEEK_RAY_ORDER=reference selects the other at run time).
+// kNearestFirst = false walks the BVH in the reference's visiting order (ties resolved
+// identically); true is the flat nearest-first query and the default (hs_sim.cu: HIDESEEK_RAY_ORDER=reference selects the other at run time).
 template <bool kNearestFirst>
 __device__ __forceinline__ int traceRaySel(const uint32_t *blob, const AssetTable &AT, bool active,
                                            Vec3 o, Vec3 d, float t_max, float *out_t)
 {
-    if (kNearestFirst) return traceRayWarpOrdered(blob, AT, active, o, d, t_max, out_t);
+    if (kNearestFirst) return traceRayFlat(blob, AT, active, o, d, t_max, out_t);
     return traceRayWarp(blob, AT, active, o, d, t_max, out_t);
 }
 
@@ -286,7 +281,8 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(g);
         uint4 *dst = reinterpret_cast<uint4 *>(sm.bvh);
-        const int nodeVec = (kBvhNodeOff + numNodes * kNodeWords) / 4;
+        // the flat query never touches the inner nodes: header only
+        const int nodeVec = kNearestFirst ? kBvhNodeOff / 4 : (kBvhNodeOff + numNodes * kNodeWords) / 4;
         for (int i = tid; i < nodeVec; i += kRayThreads) dst[i] = src[i];
         const int leafVec0 = kBvhLeafOff / 4, leafVec = (numLeaves * kLeafWords) / 4;
         for (int i = tid; i < leafVec; i += kRayThreads) dst[leafVec0 + i] = src[leafVec0 + i];
