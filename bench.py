@@ -99,9 +99,8 @@ def kernel_alg_bytes(name, A, E, C, K):
     pose, posevel = 28, 52
     table = {
         "k_move": A * (20 + 16 + 24),
-        "k_leaf_update": E * (40 + 12 + 4 + 24 + 40),
+        "k_leaf_refit": E * (40 + 12 + 4 + 24 + 40),     # pose+scale+meta+vel in, leaf record out
         "k_bvh_rebuild": 0,
-        "k_refit": E * 24,
         "k_action": A * (20 + 20),
         "k_broadphase": E * (24 + 4) + C * 2,
         "k_substep": E * (posevel + 24 + 4 + pose + 2 * pose + 24),

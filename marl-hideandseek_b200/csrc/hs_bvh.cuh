@@ -38,47 +38,6 @@ __device__ __forceinline__ const float *leafF(const uint32_t *blob, int l)
     return reinterpret_cast<const float *>(blob + kBvhLeafOff + l * kLeafWords);
 }
 
-// updateLeafPositionsEntry: one thread per (slot, world), world fastest.
-__global__ void k_leaf_update(DeviceState S)
-{
-    const int N = S.p.numWorlds;
-    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)kMaxBodies * N) return;
-    int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
-    if (s >= WI(S, WF_NUM_BODIES, w)) return;
-
-    uint32_t m = META(S, s, w);
-    const Pose pose = loadPose(S, REC_POSE, s, w);
-    Vec3 pos = pose.x;
-    Quat rot = pose.q;
-    Vec3 scale = loadScale(S, s, w);
-    float4 vel4 = recPtr(S, REC_VEL, s, w)[0];
-    Vec3 vel = {vel4.x, vel4.y, vel4.z};
-
-    AABB box = aabbApplyTRS(objAABB(metaObj(m)), pos, rot, scale);
-
-    // physics.cpp:104-111: velocity expansion 2*dt, accel expansion 100*dt*dt
-    const float vexp = 2.f * kDeltaT;
-    const float aexp = 100.f * kDeltaT * kDeltaT;
-    float lo[3] = {box.lo.x, box.lo.y, box.lo.z};
-    float hi[3] = {box.hi.x, box.hi.y, box.hi.z};
-    float v[3] = {vel.x, vel.y, vel.z};
-#pragma unroll
-    for (int i = 0; i < 3; i++) {
-        float pd = vexp * v[i];
-        float mn = pd - aexp, mx = pd + aexp;
-        if (mn < 0.f) lo[i] += mn;
-        if (mx > 0.f) hi[i] += mx;
-    }
-
-    float *L = leafF(BVH(S, w), metaLeaf(m));
-    L[0] = lo[0]; L[1] = lo[1]; L[2] = lo[2];
-    L[3] = hi[0]; L[4] = hi[1]; L[5] = hi[2];
-    L[kLeafPos + 0] = pos.x; L[kLeafPos + 1] = pos.y; L[kLeafPos + 2] = pos.z;
-    L[kLeafRot + 0] = rot.w; L[kLeafRot + 1] = rot.x; L[kLeafRot + 2] = rot.y; L[kLeafRot + 3] = rot.z;
-    L[kLeafScale + 0] = scale.x; L[kLeafScale + 1] = scale.y; L[kLeafScale + 2] = scale.z;
-}
-
 __device__ __forceinline__ float atomicMinF(float *addr, float v)
 {
     if (!signbit(v)) return __int_as_float(atomicMin((int *)addr, __float_as_int(v)));
@@ -90,23 +49,58 @@ __device__ __forceinline__ float atomicMaxF(float *addr, float v)
     return __uint_as_float(atomicMin((unsigned int *)addr, __float_as_uint(v)));
 }
 
-// refitEntry: one thread per (leaf, world).  min/max are exact and commutative,
-// and a node slot always encloses its subtree, so the result is independent of
-// the order leaves are processed in (sequential on the CPU).
-__global__ void k_refit(DeviceState S)
+// updateLeafPositionsEntry + refitEntry fused: one thread per (slot, world).  The thread that
+// recomputes a body's (velocity-expanded) leaf box also grows the node slots above it, so the
+// box never makes a round trip through HBM.  min/max are exact and commutative and a node slot
+// always encloses its subtree, so the result does not depend on the order leaves are processed
+// in (sequential on the CPU).  Worlds whose tree is about to be rebuilt (force_rebuild, set by a
+// reset) only refresh their leaf records: the rebuild that follows recomputes every node and the
+// reference's refit after a rebuild finds nothing to grow.
+// onlyIfReset: the third BVH update of a step (after resetSystem) sees unchanged bodies in every
+// world that did not reset, so it is skipped there.
+__global__ void k_leaf_refit(DeviceState S, bool onlyIfReset)
 {
     const int N = S.p.numWorlds;
     long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)kMaxBodies * N) return;
-    int l = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
+    int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
+    if (s >= WI(S, WF_NUM_BODIES, w)) return;
+    if (onlyIfReset && WI(S, WF_DID_RESET, w) == 0) return;
+
+    uint32_t m = META(S, s, w);
+    const Pose pose = loadPose(S, REC_POSE, s, w);
+    Vec3 pos = pose.x;
+    Quat rot = pose.q;
+    Vec3 scale = loadScale(S, s, w);
+    float4 vel4 = recPtr(S, REC_VEL, s, w)[0];
+
+    AABB box = aabbApplyTRS(objAABB(metaObj(m)), pos, rot, scale);
+
+    // physics.cpp:104-111: velocity expansion 2*dt, accel expansion 100*dt*dt
+    const float vexp = 2.f * kDeltaT;
+    const float aexp = 100.f * kDeltaT * kDeltaT;
+    float a[6] = {box.lo.x, box.lo.y, box.lo.z, box.hi.x, box.hi.y, box.hi.z};
+    float v[3] = {vel4.x, vel4.y, vel4.z};
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        float pd = vexp * v[i];
+        float mn = pd - aexp, mx = pd + aexp;
+        if (mn < 0.f) a[i] += mn;
+        if (mx > 0.f) a[3 + i] += mx;
+    }
+
     uint32_t *blob = BVH(S, w);
-    if (l >= (int)blob[1]) return;
+    float4 *L4 = reinterpret_cast<float4 *>(blob + kBvhLeafOff + metaLeaf(m) * kLeafWords);
+    const float4 keep = L4[1];                       // .z = parent word, .w = slot | obj << 8
+    L4[0] = make_float4(a[0], a[1], a[2], a[3]);
+    L4[1] = make_float4(a[4], a[5], keep.z, keep.w);
+    L4[2] = make_float4(pos.x, pos.y, pos.z, rot.w);
+    L4[3] = make_float4(rot.x, rot.y, rot.z, scale.x);
+    L4[4] = make_float4(scale.y, scale.z, 0.f, 0.f);
+    if (blob[2] != 0) return;                        // rebuild pending
 
-    const float *L = leafF(blob, l);
-    float a[6] = {L[0], L[1], L[2], L[3], L[4], L[5]};
-    uint32_t lp = blob[kBvhLeafOff + l * kLeafWords + kLeafParent];
+    const uint32_t lp = __float_as_uint(keep.z);
     int node = int(lp >> 2), sub = int(lp & 3);
-
     bool expanded = false;
     {
         float *nf = nodeF(blob, node);

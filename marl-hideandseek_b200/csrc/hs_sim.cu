@@ -340,12 +340,12 @@ struct Launcher {
     dim3 gWarpAgent(int block = 128) const { return dim3(unsigned(((long long)N() * S.p.agentsPerWorld * 32 + block - 1) / block)); }
 };
 
-// setupBVHTasks (broadphase.cpp:995-1017): update leaves, rebuild if forced, refit
-void launchBroadphaseSetup(Launcher &L, bool mayRebuild)
+// setupBVHTasks (broadphase.cpp:995-1017): update leaves, rebuild if forced, refit.  Leaf update
+// and refit are one kernel; the rebuild of freshly reset worlds follows it (see k_leaf_refit).
+void launchBroadphaseSetup(Launcher &L, bool mayRebuild, bool onlyIfReset = false)
 {
-    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_leaf_update");
+    k_leaf_refit<<<L.gBody(), 256, 0, L.st>>>(L.S, onlyIfReset); L.mark("k_leaf_refit");
     if (mayRebuild) { k_bvh_rebuild<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_bvh_rebuild"); }
-    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_refit");
 }
 
 // observationsTasks (src/sim.cpp:1232-1293)
@@ -362,7 +362,7 @@ void launchObservations(Launcher &L, float cosThr, bool nearestFirst)
 void launchStep(Launcher &L, float cosThr, bool nearestFirst)
 {
     k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.mark("k_move");
-    launchBroadphaseSetup(L, true);
+    launchBroadphaseSetup(L, false);       // a rebuild is only ever pending right after a reset
     k_action<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_action");
     k_broadphase<<<(L.N() + kBroadWarps - 1) / kBroadWarps, kBroadWarps * 32, 0, L.st>>>(L.S); L.mark("k_broadphase");
     for (int i = 0; i < kSubsteps; i++) {
@@ -372,8 +372,7 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
         k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_set_velocities");
         k_solve_velocities<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_velocities");
     }
-    k_leaf_update<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_leaf_update");
-    k_refit<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_refit");
+    launchBroadphaseSetup(L, false);
     if (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) {
         k_zero_agent_vel<<<dim3((L.N() * kMaxAgents + 127) / 128), 128, 0, L.st>>>(L.S); L.mark("k_zero_agent_vel");
     }
@@ -381,7 +380,7 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
     else k_rewards<false><<<(L.N() + kRewardWarps - 1) / kRewardWarps, kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
     L.mark("k_rewards");
     k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_reset");
-    launchBroadphaseSetup(L, true);
+    launchBroadphaseSetup(L, true, (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) == 0);
     launchObservations(L, cosThr, nearestFirst);
 }
 
