@@ -253,6 +253,26 @@ __global__ void k_bvh_rebuild(DeviceState S)
         pi[kNodeChild + off] = nodeId;
         for (int k = 0; k < 6; k++) pf[k * 4 + off] = c[k];
     }
+
+    // Leaves in the order BVH::findIntersecting meets them (LIFO stack, children 0..3, leaves
+    // reported as soon as their node is popped — M/include/madrona/broadphase.inl:22-59).  A pruned
+    // walk reports a subset of the leaves in this same relative order, which is all k_broadphase
+    // needs to emit candidate pairs in the reference's order without walking the tree.
+    {
+        uint8_t *dfs = S.dfsLeaf + size_t(w) * kDfsStride;
+        int32_t st[32];
+        st[0] = 0;
+        int sp = 1, n = 0;
+        while (sp > 0) {
+            const int32_t *ni = nodeI(blob, st[--sp]);
+            for (int i = 0; i < 4; i++) {
+                int32_t child = ni[kNodeChild + i];
+                if (child == kSentinel) continue;
+                if (child < 0) { if (n < kMaxBodies) dfs[n++] = uint8_t(child & 0x7FFFFFFF); }
+                else if (sp < 32) st[sp++] = child;
+            }
+        }
+    }
 }
 
 }  // namespace hs

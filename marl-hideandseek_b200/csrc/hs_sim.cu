@@ -104,6 +104,7 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     HS_TRY(devAlloc(sim, &S.joint, size_t(JF_COUNT) * kMaxAgents * N));
     HS_TRY(devAlloc(sim, &S.jmeta, size_t(kMaxAgents) * N));
     HS_TRY(devAlloc(sim, &S.bvh, size_t(kBvhWords) * N));
+    HS_TRY(devAlloc(sim, &S.dfsLeaf, size_t(kDfsStride) * N));
     HS_TRY(devAlloc(sim, &S.cand, size_t(kMaxCand) * N));
     HS_TRY(devAlloc(sim, &S.contact, size_t(kMaxCand) * kContactWords * N));
     HS_TRY(devAlloc(sim, &S.cmeta, size_t(kMaxCand) * N));

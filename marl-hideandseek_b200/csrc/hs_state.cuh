@@ -141,6 +141,7 @@ constexpr int kBvhWords = kBvhLeafOff + kMaxBodies * kLeafWords;   // 3252 words
 constexpr int kNodeChild = 24, kNodeParent = 28;
 constexpr int kLeafParent = 6, kLeafInfo = 7, kLeafPos = 8, kLeafRot = 11, kLeafScale = 15;
 constexpr int32_t kSentinel = -1;    // 0xFFFFFFFF
+constexpr int kDfsStride = 64;       // bytes per world of the leaf visiting-order table
 
 // ---- contacts (world-major) ----------------------------------------------------
 constexpr int kContactWords = 20;    // points[4]{x,y,z,depth} normal[3] lambdaN
@@ -189,6 +190,7 @@ struct DeviceState {
     float *joint;            // [JF_COUNT][kMaxAgents][N]
     uint32_t *jmeta;         // [kMaxAgents][N]
     uint32_t *bvh;           // [N][kBvhWords]
+    uint8_t *dfsLeaf;        // [N][kDfsStride] leaf ids in BVH visiting order (set by the rebuild)
     uint16_t *cand;          // [N][kMaxCand]  a | b<<8
     float *contact;          // [N][kMaxCand][kContactWords]
     uint32_t *cmeta;         // [N][kMaxCand]
@@ -229,6 +231,7 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
     V.p.worldBase = S.p.worldBase + begin;
     V.body += b * kMaxBodies * kBodyWords; V.meta += b * kMaxBodies; V.wi += b; V.wb += b; V.joint += b; V.jmeta += b;
     V.bvh += b * kBvhWords;
+    V.dfsLeaf += b * kDfsStride;
     V.cand += b * kMaxCand;
     V.contact += b * kMaxCand * kContactWords;
     V.cmeta += b * kMaxCand;

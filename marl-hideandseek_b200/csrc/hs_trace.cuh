@@ -134,47 +134,29 @@ __device__ __forceinline__ void forEachOverlap(const uint32_t *blob, const AABB 
     }
 }
 
-// findIntersectingEntry: one warp per world, lanes own bodies {lane, lane+32}.  The world's BVH
-// nodes, leaf->slot map and body meta words are staged in shared memory (one coalesced copy)
-// because every lane walks the same small tree.  Pass 1 counts each body's emitted pairs, a
-// warp scan turns counts into offsets in body-row order, pass 2 re-walks and writes — so the
-// candidate list is in exactly the order the sequential reference produces it.
+// findIntersectingEntry: one warp per world, lanes own bodies {lane, lane+32}.
+//
+// The reference walks the BVH once per body and emits a pair for every leaf whose stored node
+// slot overlaps the body's leaf box.  Node slots nest (a slot encloses everything below it, both
+// after a rebuild and under grow-only refit), so "the walk reaches leaf l" is equivalent to "the
+// query overlaps l's own slot in its parent node", and a pruned walk reports leaves in the same
+// relative order as the full walk.  So instead of 29 divergent tree walks per world the warp
+// stages, in visiting order (dfsLeaf, written by the rebuild), each leaf's slot bounds, body slot
+// and meta word in shared memory, and every lane runs ONE uniform loop over that list —
+// broadcast reads, no divergence — collecting its hits in a 64-bit mask.  A warp scan of the
+// popcounts gives each body its offset in body-row order and the set bits are written out in
+// visiting order: the candidate list is exactly the sequential reference's.
 constexpr int kBroadWarps = 4;
 
 struct alignas(16) BroadWarpSmem {
-    uint32_t nodes[kBvhNodeOff + kMaxNodes * kNodeWords];    // header + nodes, blob layout
-    uint32_t meta[kMaxBodies];
-    uint8_t leafSlot[kMaxBodies + 4];
+    float bounds[6][kDfsStride];     // slot bounds of the r-th visited leaf
+    uint32_t meta[kDfsStride];       // meta word of the body in that leaf
+    uint8_t slot[kDfsStride];
 };
-
-template <typename Fn>
-__device__ __forceinline__ void forEachOverlapS(const BroadWarpSmem &ws, const AABB &q, Fn &&fn)
-{
-    uint8_t stack[24];
-    stack[0] = 0;
-    int sp = 1;
-    while (sp > 0) {
-        int node = stack[--sp];
-        const float4 *nf = reinterpret_cast<const float4 *>(ws.nodes + kBvhNodeOff + node * kNodeWords);
-        const float4 lox = nf[0], loy = nf[1], loz = nf[2], hix = nf[3], hiy = nf[4], hiz = nf[5];
-        const int4 ch = *reinterpret_cast<const int4 *>(ws.nodes + kBvhNodeOff + node * kNodeWords + kNodeChild);
-#define HS_OVL(C, LX, LY, LZ, HX, HY, HZ)                                                     \
-        if (C != kSentinel && q.lo.x < HX && LX < q.hi.x && q.lo.y < HY && LY < q.hi.y &&     \
-            q.lo.z < HZ && LZ < q.hi.z) {                                                      \
-            if (C < 0) fn(int(ws.leafSlot[C & 0x7FFFFFFF]));                                   \
-            else if (sp < 24) stack[sp++] = (uint8_t)C;                                        \
-        }
-        HS_OVL(ch.x, lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x)
-        HS_OVL(ch.y, lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y)
-        HS_OVL(ch.z, lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z)
-        HS_OVL(ch.w, lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w)
-#undef HS_OVL
-    }
-}
 
 __global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
 {
-    __shared__ __align__(16) BroadWarpSmem sm[kBroadWarps];
+    __shared__ BroadWarpSmem sm[kBroadWarps];
     const int lane = threadIdx.x & 31;
     const int w = blockIdx.x * kBroadWarps + (threadIdx.x >> 5);
     if (w >= S.p.numWorlds) return;
@@ -182,49 +164,55 @@ __global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
 
     const uint32_t *blob = BVH(S, w);
     const int nb = WI(S, WF_NUM_BODIES, w);
-    {
-        const int numNodes = min((int)blob[0], kMaxNodes), numLeaves = min((int)blob[1], kMaxBodies);
-        const uint4 *src = reinterpret_cast<const uint4 *>(blob);
-        uint4 *dst = reinterpret_cast<uint4 *>(ws.nodes);
-        const int nvec = (kBvhNodeOff + numNodes * kNodeWords) / 4;
-        for (int i = lane; i < nvec; i += 32) dst[i] = src[i];
-        for (int l = lane; l < numLeaves; l += 32)
-            ws.leafSlot[l] = (uint8_t)(blob[kBvhLeafOff + l * kLeafWords + kLeafInfo] & 0xFF);
-        for (int s = lane; s < nb; s += 32) ws.meta[s] = META(S, s, w);
+    const int numLeaves = min((int)blob[1], kMaxBodies);
+    const uint8_t *dfs = S.dfsLeaf + size_t(w) * kDfsStride;
+    for (int r = lane; r < numLeaves; r += 32) {
+        const int leaf = dfs[r];
+        const uint32_t lp = blob[kBvhLeafOff + leaf * kLeafWords + kLeafParent];
+        const float *nf = nodeF(blob, int(lp >> 2));
+        const int sub = int(lp & 3);
+#pragma unroll
+        for (int k = 0; k < 6; k++) ws.bounds[k][r] = nf[k * 4 + sub];
+        const int slot = int(blob[kBvhLeafOff + leaf * kLeafWords + kLeafInfo] & 0xFF);
+        ws.slot[r] = (uint8_t)slot;
+        ws.meta[r] = META(S, slot, w);
     }
     __syncwarp();
 
+    unsigned long long hits[2] = {0ull, 0ull};
     int counts[2] = {0, 0};
-    uint32_t metas[2];
-    AABB boxes[2];
-    for (int r = 0; r < 2; r++) {
-        int s = lane + 32 * r;
+    for (int rd = 0; rd < 2; rd++) {
+        const int s = lane + 32 * rd;
         if (s >= nb) continue;
-        uint32_t m = ws.meta[s];
-        metas[r] = m;
+        const uint32_t m = META(S, s, w);
         const float *L = leafF(blob, metaLeaf(m));
-        boxes[r] = {{L[0], L[1], L[2]}, {L[3], L[4], L[5]}};
-        int eid = metaEid(m);
-        bool aStatic = metaResp(m) == RESP_STATIC;
-        int c = 0;
-        forEachOverlapS(ws, boxes[r], [&](int other) {
-            uint32_t mo = ws.meta[other];
-            if (eid < metaEid(mo) && !(aStatic && metaResp(mo) == RESP_STATIC)) c++;
-        });
-        counts[r] = c;
+        const float qlx = L[0], qly = L[1], qlz = L[2], qhx = L[3], qhy = L[4], qhz = L[5];
+        const int eid = metaEid(m);
+        const bool aStatic = metaResp(m) == RESP_STATIC;
+        unsigned long long h = 0ull;
+        for (int r = 0; r < numLeaves; r++) {
+            // AABB::overlaps(query, slot) — strict
+            const bool ov = qlx < ws.bounds[3][r] && ws.bounds[0][r] < qhx &&
+                            qly < ws.bounds[4][r] && ws.bounds[1][r] < qhy &&
+                            qlz < ws.bounds[5][r] && ws.bounds[2][r] < qhz;
+            const uint32_t mo = ws.meta[r];
+            if (ov && eid < metaEid(mo) && !(aStatic && metaResp(mo) == RESP_STATIC)) h |= 1ull << r;
+        }
+        hits[rd] = h;
+        counts[rd] = __popcll(h);
     }
 
     int offs[2];
     int base = 0;
-    for (int r = 0; r < 2; r++) {
-        int v = counts[r];
+    for (int rd = 0; rd < 2; rd++) {
+        int v = counts[rd];
         int incl = v;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             int t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
             if (lane >= d) incl += t;
         }
-        offs[r] = base + incl - v;
+        offs[rd] = base + incl - v;
         base += __shfl_sync(0xFFFFFFFFu, incl, 31);
     }
 
@@ -236,20 +224,16 @@ __global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
     if (lane == 0) WI(S, WF_NUM_CAND, w) = total;
 
     uint16_t *out = S.cand + size_t(w) * kMaxCand;
-    for (int r = 0; r < 2; r++) {
-        int s = lane + 32 * r;
-        if (s >= nb || counts[r] == 0) continue;
-        uint32_t m = metas[r];
-        int eid = metaEid(m);
-        bool aStatic = metaResp(m) == RESP_STATIC;
-        int o = offs[r];
-        forEachOverlapS(ws, boxes[r], [&](int other) {
-            uint32_t mo = ws.meta[other];
-            if (eid < metaEid(mo) && !(aStatic && metaResp(mo) == RESP_STATIC)) {
-                if (o < kMaxCand) out[o] = uint16_t(s | (other << 8));
-                o++;
-            }
-        });
+    for (int rd = 0; rd < 2; rd++) {
+        const int s = lane + 32 * rd;
+        unsigned long long h = hits[rd];
+        int o = offs[rd];
+        while (h) {
+            const int r = __ffsll((long long)h) - 1;
+            h &= h - 1ull;
+            if (o < kMaxCand) out[o] = uint16_t(s | (int(ws.slot[r]) << 8));
+            o++;
+        }
     }
 }
 
