@@ -1,6 +1,5 @@
-// Observation stages: relative observations, visibility masks, 30-ray lidar,
-// global debug positions.  One warp per agent-interface row; lanes own
-// entities (obs / visibility) or rays (lidar).
+// Observation stages: relative observations and global debug positions (visibility masks and
+// the 30-ray lidar live in hs_rays.cuh).
 //
 // Behavioural contract:
 //   collectObservationsSystem / computeRelativePosVelObs / quatToEuler /
@@ -48,159 +47,116 @@ __device__ __forceinline__ void writeRelObs(float *out, Vec3 origin, Quat toFram
 // the reference's enumeration (skip self, pad to maxAgents-1 with empty slots).
 __device__ __forceinline__ int otherAgentIndex(int self, int other) { return other < self ? other : other - 1; }
 
+// collectObservationsSystem.  One thread per output record, records grouped BY KIND across the
+// whole slice — [R self rows][R*9 box records][R*2 ramp records][R*6 other-agent records] — so
+// a warp runs a single code path (the euler-angle math is ~200 instructions and the four kinds
+// differ) and consecutive threads write consecutive records.
+struct ObsFrame { Vec3 pos; Quat toFrame; Vec3 vel, ang; };
+
+__device__ __forceinline__ ObsFrame obsFrame(const DeviceState &S, int slot, int w)
+{
+    const Pose p = loadPose(S, REC_POSE, slot, w);
+    const Vel6 v = loadVel6(S, REC_VEL, slot, w);
+    return {p.x, qinv(p.q), v.v, v.w};
+}
+
+__device__ __forceinline__ void writeRelObsOf(float *o, const ObsFrame &F, const DeviceState &S, int b, int w)
+{
+    const Pose p = loadPose(S, REC_POSE, b, w);
+    const Vel6 v = loadVel6(S, REC_VEL, b, w);
+    writeRelObs(o, F.pos, F.toFrame, F.vel, F.ang, p.x, p.q, v.v, v.w);
+}
+
 __global__ void k_observations(DeviceState S)
 {
     const int A = S.p.agentsPerWorld;
-    const int lane = threadIdx.x & 31;
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (row >= S.p.numWorlds * A) return;
-    const int w = row / A, k = row % A;
-    const int slot = WB(S, WB_IFACE_SLOT + k, w);
-    if (slot == 0xFF) return;
+    const long long R = (long long)S.p.numWorlds * A;
+    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= R * 18) return;
 
-    const int curStep = WI(S, WF_EPISODE_STEP, w);
-    const int nDyn = WI(S, WF_NUM_DYN, w);
-    Vec3 apos = loadPos(S, slot, w);
-    Quat arot = loadRot(S, slot, w);
-    Vec3 avel = loadV3(S, BF_VX, slot, w), aang = loadV3(S, BF_WX, slot, w);
-    Quat toFrame = qinv(arot);
-
-    if (lane == 0) {
+    if (idx < R) {
+        // ---- self observation + prep counter ---------------------------------------------------
+        const int row = int(idx), w = row / A, k = row % A;
+        const int slot = WB(S, WB_IFACE_SLOT + k, w);
+        if (slot == 0xFF) return;
+        const int curStep = WI(S, WF_EPISODE_STEP, w);
         if (curStep <= kNumPrepSteps) S.exPrepCounter[row] = kNumPrepSteps - curStep;
+        const Pose p = loadPose(S, REC_POSE, slot, w);
+        const Vel6 v = loadVel6(S, REC_VEL, slot, w);
+        const Quat toFrame = qinv(p.q);
         float *o = S.exSelfObs + size_t(row) * 13;
-        Vec3 e = quatToEuler(arot);
-        Vec3 lv = rotate(toFrame, avel), av = rotate(toFrame, aang);
-        o[0] = apos.x; o[1] = apos.y; o[2] = apos.z;
+        Vec3 e = quatToEuler(p.q);
+        Vec3 lv = rotate(toFrame, v.v), av = rotate(toFrame, v.w);
+        o[0] = p.x.x; o[1] = p.x.y; o[2] = p.x.z;
         o[3] = e.x; o[4] = e.y; o[5] = e.z;
         o[6] = lv.x; o[7] = lv.y; o[8] = lv.z;
         o[9] = av.x; o[10] = av.y; o[11] = av.z;
-        o[12] = JMETA(S, slot - nDyn, w) != 0xFFFFFFFFu ? 1.f : 0.f;
-    } else if (lane <= kMaxBoxes) {
-        int i = lane - 1;
-        float *o = S.exBoxObs + (size_t(row) * kMaxBoxes + i) * 17;
+        o[12] = JMETA(S, slot - WI(S, WF_NUM_DYN, w), w) != 0xFFFFFFFFu ? 1.f : 0.f;
+        return;
+    }
+    idx -= R;
+    if (idx < R * kMaxBoxes) {
+        // ---- boxes ------------------------------------------------------------------------------
+        const int row = int(idx / kMaxBoxes), i = int(idx % kMaxBoxes), w = row / A, k = row % A;
+        const int slot = WB(S, WB_IFACE_SLOT + k, w);
+        if (slot == 0xFF) return;
+        float *o = S.exBoxObs + size_t(idx) * 17;
         if (i >= WI(S, WF_NUM_BOXES, w)) {
             for (int c = 0; c < 17; c++) o[c] = 0.f;
-        } else {
-            int b = WB(S, WB_BOX_SLOT + i, w);
-            uint32_t m = META(S, b, w);
-            writeRelObs(o, apos, toFrame, avel, aang, loadPos(S, b, w), loadRot(S, b, w),
-                        loadV3(S, BF_VX, b, w), loadV3(S, BF_WX, b, w));
-            bool elongated = metaObj(m) == OBJ_BOX;     // boxSizes, level_gen.cpp:150,191
-            o[12] = elongated ? 8.f : 2.f; o[13] = elongated ? 1.5f : 2.f; o[14] = 2.f;
-            bool locked = metaResp(m) == RESP_STATIC;
-            bool hider = metaOwner(m) == OWNER_HIDER;
-            o[15] = locked && hider ? 1.f : 0.f;
-            o[16] = locked && !hider ? 1.f : 0.f;
+            return;
         }
-    } else if (lane <= kMaxBoxes + kMaxRamps) {
-        int i = lane - 1 - kMaxBoxes;
-        float *o = S.exRampObs + (size_t(row) * kMaxRamps + i) * 14;
+        const int b = WB(S, WB_BOX_SLOT + i, w);
+        const uint32_t m = META(S, b, w);
+        writeRelObsOf(o, obsFrame(S, slot, w), S, b, w);
+        bool elongated = metaObj(m) == OBJ_BOX;     // boxSizes, level_gen.cpp:150,191
+        o[12] = elongated ? 8.f : 2.f; o[13] = elongated ? 1.5f : 2.f; o[14] = 2.f;
+        bool locked = metaResp(m) == RESP_STATIC;
+        bool hider = metaOwner(m) == OWNER_HIDER;
+        o[15] = locked && hider ? 1.f : 0.f;
+        o[16] = locked && !hider ? 1.f : 0.f;
+        return;
+    }
+    idx -= R * kMaxBoxes;
+    if (idx < R * kMaxRamps) {
+        // ---- ramps ------------------------------------------------------------------------------
+        const int row = int(idx / kMaxRamps), i = int(idx % kMaxRamps), w = row / A, k = row % A;
+        const int slot = WB(S, WB_IFACE_SLOT + k, w);
+        if (slot == 0xFF) return;
+        float *o = S.exRampObs + size_t(idx) * 14;
         if (i >= WI(S, WF_NUM_RAMPS, w)) {
             for (int c = 0; c < 14; c++) o[c] = 0.f;
-        } else {
-            int b = WB(S, WB_RAMP_SLOT + i, w);
-            uint32_t m = META(S, b, w);
-            writeRelObs(o, apos, toFrame, avel, aang, loadPos(S, b, w), loadRot(S, b, w),
-                        loadV3(S, BF_VX, b, w), loadV3(S, BF_WX, b, w));
-            bool locked = metaResp(m) == RESP_STATIC;
-            bool hider = metaOwner(m) == OWNER_HIDER;
-            o[12] = locked && hider ? 1.f : 0.f;
-            o[13] = locked && !hider ? 1.f : 0.f;
+            return;
         }
-    } else if (lane <= kMaxBoxes + kMaxRamps + kMaxAgents) {
-        int j = lane - 1 - kMaxBoxes - kMaxRamps;     // interface index 0..5
-        int numAgents = WI(S, WF_NUM_AGENTS, w);
+        const int b = WB(S, WB_RAMP_SLOT + i, w);
+        const uint32_t m = META(S, b, w);
+        writeRelObsOf(o, obsFrame(S, slot, w), S, b, w);
+        bool locked = metaResp(m) == RESP_STATIC;
+        bool hider = metaOwner(m) == OWNER_HIDER;
+        o[12] = locked && hider ? 1.f : 0.f;
+        o[13] = locked && !hider ? 1.f : 0.f;
+        return;
+    }
+    idx -= R * kMaxRamps;
+    {
+        // ---- other agents: interface index j = 0..5 (src/sim.cpp:527-564: active others first,
+        // skipping self, then one empty entry per inactive index) ---------------------------------
+        const int row = int(idx / kMaxAgents), j = int(idx % kMaxAgents), w = row / A, k = row % A;
+        const int slot = WB(S, WB_IFACE_SLOT + k, w);
+        if (slot == 0xFF) return;
+        const int numAgents = WI(S, WF_NUM_AGENTS, w);
         if (j == k && j < numAgents) return;
-        // enumeration of src/sim.cpp:527-564: active others first (skipping self),
-        // then one empty entry per inactive index
-        int outIdx = j < numAgents ? otherAgentIndex(k, j) : j - 1;
+        const int outIdx = j < numAgents ? otherAgentIndex(k, j) : j - 1;
         if (outIdx < 0 || outIdx >= kMaxAgents - 1) return;
         float *o = S.exAgentObs + (size_t(row) * (kMaxAgents - 1) + outIdx) * 14;
         if (j >= numAgents) {
             for (int c = 0; c < 14; c++) o[c] = 0.f;
-        } else {
-            int b = WB(S, WB_IFACE_SLOT + j, w);
-            writeRelObs(o, apos, toFrame, avel, aang, loadPos(S, b, w), loadRot(S, b, w),
-                        loadV3(S, BF_VX, b, w), loadV3(S, BF_WX, b, w));
-            o[12] = WB(S, WB_IFACE_TYPE + j, w) == AGENT_HIDER ? 1.f : 0.f;
-            o[13] = JMETA(S, b - nDyn, w) != 0xFFFFFFFFu ? 1.f : 0.f;
+            return;
         }
+        const int b = WB(S, WB_IFACE_SLOT + j, w);
+        writeRelObsOf(o, obsFrame(S, slot, w), S, b, w);
+        o[12] = WB(S, WB_IFACE_TYPE + j, w) == AGENT_HIDER ? 1.f : 0.f;
+        o[13] = JMETA(S, b - WI(S, WF_NUM_DYN, w), w) != 0xFFFFFFFFu ? 1.f : 0.f;
     }
-}
-
-__global__ void k_visibility(DeviceState S, float cosThreshold)
-{
-    const int A = S.p.agentsPerWorld;
-    const int lane = threadIdx.x & 31;
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (row >= S.p.numWorlds * A) return;
-    const int w = row / A, k = row % A;
-    const int slot = WB(S, WB_IFACE_SLOT + k, w);
-    if (slot == 0xFF) return;
-
-    const uint32_t *blob = BVH(S, w);
-    Vec3 apos = loadPos(S, slot, w);
-    Vec3 afwd = rotate(loadRot(S, slot, w), v3(0, 1, 0));
-
-    auto visible = [&](int other) {
-        Vec3 to = loadPos(S, other, w) - apos;
-        float cosA = dot(normalize(to), afwd);
-        if (cosA < cosThreshold) return 0.f;
-        float t;
-        return traceRay(blob, apos, to, 1.f, &t) == other ? 1.f : 0.f;
-    };
-
-    if (lane < kMaxBoxes) {
-        float v = 0.f;
-        if (lane < WI(S, WF_NUM_BOXES, w)) v = visible(WB(S, WB_BOX_SLOT + lane, w));
-        S.exBoxVis[size_t(row) * kMaxBoxes + lane] = v;
-    } else if (lane < kMaxBoxes + kMaxRamps) {
-        int i = lane - kMaxBoxes;
-        float v = 0.f;
-        if (i < WI(S, WF_NUM_RAMPS, w)) v = visible(WB(S, WB_RAMP_SLOT + i, w));
-        S.exRampVis[size_t(row) * kMaxRamps + i] = v;
-    } else if (lane < kMaxBoxes + kMaxRamps + kMaxAgents) {
-        int j = lane - kMaxBoxes - kMaxRamps;
-        int numAgents = WI(S, WF_NUM_AGENTS, w);
-        if (j == k && j < numAgents) return;
-        int outIdx = j < numAgents ? otherAgentIndex(k, j) : j - 1;
-        if (outIdx < 0 || outIdx >= kMaxAgents - 1) return;
-        float v = 0.f;
-        if (j < numAgents) {
-            v = visible(WB(S, WB_IFACE_SLOT + j, w));
-            // CPU-backend side effect (src/sim.cpp:700-705)
-            if (v == 1.f && WB(S, WB_IFACE_TYPE + k, w) == AGENT_SEEKER &&
-                WB(S, WB_IFACE_TYPE + j, w) == AGENT_HIDER) {
-                WI(S, WF_HIDER_REWARD, w) = __float_as_int(-1.f);
-            }
-        }
-        S.exAgentVis[size_t(row) * (kMaxAgents - 1) + outIdx] = v;
-    }
-}
-
-__global__ void k_lidar(DeviceState S)
-{
-    const int A = S.p.agentsPerWorld;
-    const int lane = threadIdx.x & 31;
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (row >= S.p.numWorlds * A) return;
-    const int w = row / A, k = row % A;
-    const int slot = WB(S, WB_IFACE_SLOT + k, w);
-    if (slot == 0xFF || lane >= 30) return;
-
-    const float pi = 3.14159265358979323846f;
-    Vec3 pos = loadPos(S, slot, w);
-    Quat rot = loadRot(S, slot, w);
-    Vec3 fwd = rotate(rot, v3(0, 1, 0));
-    Vec3 right = rotate(rot, v3(1, 0, 0));
-
-    float theta = 2.f * pi * (float(lane) / float(30)) + pi / 2.f;
-    float x, y;
-    hs_det_sincosf(theta, &y, &x);
-    Vec3 dir = normalize(x * right + y * fwd);
-    float t;
-    int hit = traceRay(BVH(S, w), pos, dir, 200.f, &t);
-    S.exLidar[size_t(row) * 30 + lane] = hit < 0 ? 0.f : t;
 }
 
 __global__ void k_debug_positions(DeviceState S)

@@ -394,10 +394,13 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
 }
 
 // rewardsVisSystem + outputRewardsDonesSystem + updateEpisodeResultsSystem (src/sim.cpp:763-893).
-// One warp per world: lane = (seeker, hider) pair for the occlusion rays — the reference's early
-// `break` only skips work, "any seeker sees any hider" is order-free — then lanes < A write the
-// per-agent reward / done rows and lane 0 the per-world episode result.
+// A world has at most 3 x 3 (seeker, hider) occlusion rays, so three worlds share a warp (lanes
+// 0-8, 9-17, 18-26); the reference's early `break` only skips work, "any seeker sees any hider"
+// is order-free.  Lanes < A of each group then write the per-agent reward / done rows and the
+// group's first lane the per-world episode result.
 constexpr int kRewardWarps = 4;
+constexpr int kRewardWorldsPerWarp = 3;
+constexpr int kRewardLanes = 9;
 
 template <bool kNearestFirst>
 __global__ void __launch_bounds__(kRewardWarps * 32) k_rewards(DeviceState S, float cosThreshold)
@@ -410,32 +413,39 @@ __global__ void __launch_bounds__(kRewardWarps * 32) k_rewards(DeviceState S, fl
     }
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const int w = blockIdx.x * kRewardWarps + (threadIdx.x >> 5);
-    if (w >= S.p.numWorlds) return;
+    const int grp = lane / kRewardLanes, lg = lane - grp * kRewardLanes;
+    const int warp = blockIdx.x * kRewardWarps + (threadIdx.x >> 5);
+    const int w = warp * kRewardWorldsPerWarp + grp;
+    const bool valid = grp < kRewardWorldsPerWarp && w < S.p.numWorlds;
+    const int wc = valid ? w : 0;                  // lanes without a world still join the warp votes
+    const unsigned gmask = valid ? (((1u << kRewardLanes) - 1u) << (grp * kRewardLanes)) : 0u;
     const int A = S.p.agentsPerWorld;
-    const int curStep = WI(S, WF_EPISODE_STEP, w);
-    float teamReward = __int_as_float(WI(S, WF_HIDER_REWARD, w));
-    const int numHiders = WI(S, WF_NUM_HIDERS, w), numSeekers = WI(S, WF_NUM_SEEKERS, w);
+    const int curStep = WI(S, WF_EPISODE_STEP, wc);
+    float teamReward = __int_as_float(WI(S, WF_HIDER_REWARD, wc));
+    const int numHiders = WI(S, WF_NUM_HIDERS, wc), numSeekers = WI(S, WF_NUM_SEEKERS, wc);
 
-    bool active = lane < numHiders * numSeekers;
+    bool active = valid && lg < numHiders * numSeekers;
     int hslot = -1;
     Vec3 spos = {0.f, 0.f, 0.f}, toHider = {1.f, 0.f, 0.f};
     if (active) {
-        int si = lane / numHiders, hi = lane - si * numHiders;
+        int si = lg / numHiders, hi = lg - si * numHiders;
         int sslot = WB(S, WB_SEEKER_SLOT + si, w);
         hslot = WB(S, WB_HIDER_SLOT + hi, w);
-        spos = loadPos(S, sslot, w);
-        Vec3 sfwd = rotate(loadRot(S, sslot, w), v3(0, 1, 0));
+        const Pose sp = loadPose(S, REC_POSE, sslot, w);
+        spos = sp.x;
+        Vec3 sfwd = rotate(sp.q, v3(0, 1, 0));
         toHider = loadPos(S, hslot, w) - spos;
         float cosA = dot(normalize(toHider), sfwd);
         if (cosA < cosThreshold) active = false;
     }
     float t;
-    int hit = traceRaySel<kNearestFirst>(BVH(S, w), s_assets, active, spos, toHider, 1.f, &t);
-    if (__ballot_sync(0xFFFFFFFFu, active && hit == hslot)) teamReward = -1.f;
+    int hit = traceRaySel<kNearestFirst>(BVH(S, wc), s_assets, active, spos, toHider, 1.f, &t);
+    const unsigned seen = __ballot_sync(0xFFFFFFFFu, active && hit == hslot);
+    if (!valid) return;
+    if (seen & gmask) teamReward = -1.f;
 
-    if (lane < A) {
-        const int k = lane;
+    if (lg < A) {
+        const int k = lg;
         int slot = WB(S, WB_IFACE_SLOT + k, w);
         if (slot != 0xFF) {
             size_t row = size_t(w) * A + k;
@@ -452,7 +462,7 @@ __global__ void __launch_bounds__(kRewardWarps * 32) k_rewards(DeviceState S, fl
             }
         }
     }
-    if (lane == 0) {
+    if (lg == 0) {
         WI(S, WF_HIDER_REWARD, w) = __float_as_int(teamReward);
         float *res = S.exEpisodeResult + size_t(w) * 2;
         int s0 = WI(S, WF_SCORE0, w), s1 = WI(S, WF_SCORE1, w);

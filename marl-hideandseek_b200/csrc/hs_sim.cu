@@ -352,7 +352,7 @@ void launchBroadphaseSetup(Launcher &L, bool mayRebuild, bool onlyIfReset = fals
 // observationsTasks (src/sim.cpp:1232-1293)
 void launchObservations(Launcher &L, float cosThr, bool nearestFirst)
 {
-    k_observations<<<L.gWarpAgent(), 128, 0, L.st>>>(L.S); L.mark("k_observations");
+    k_observations<<<unsigned(((long long)L.N() * L.S.p.agentsPerWorld * 18 + 255) / 256), 256, 0, L.st>>>(L.S); L.mark("k_observations");
     if (nearestFirst) k_rays<true><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
     else k_rays<false><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
     L.mark("k_rays");
@@ -377,8 +377,8 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
     if (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) {
         k_zero_agent_vel<<<dim3((L.N() * kMaxAgents + 127) / 128), 128, 0, L.st>>>(L.S); L.mark("k_zero_agent_vel");
     }
-    if (nearestFirst) k_rewards<true><<<(L.N() + kRewardWarps - 1) / kRewardWarps, kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
-    else k_rewards<false><<<(L.N() + kRewardWarps - 1) / kRewardWarps, kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
+    if (nearestFirst) k_rewards<true><<<(L.N() + kRewardWarps * kRewardWorldsPerWarp - 1) / (kRewardWarps * kRewardWorldsPerWarp), kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
+    else k_rewards<false><<<(L.N() + kRewardWarps * kRewardWorldsPerWarp - 1) / (kRewardWarps * kRewardWorldsPerWarp), kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
     L.mark("k_rewards");
     k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_reset");
     launchBroadphaseSetup(L, true, (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) == 0);
