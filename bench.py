@@ -125,6 +125,17 @@ def aggregate_value(n_per_rank, world, steps, ms_total):
     return n_per_rank * world * steps / (ms_total / 1000.0)
 
 
+def measured_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed
+    `ncu --set full` capture (profiles/traffic.json, written by tools/ncu_digest.py --traffic)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return t["kernels"].get(kernel), t.get("source")
+    except Exception:
+        return None, None
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -280,8 +291,10 @@ def run_ours(args):
                         "alg_bytes_per_launch": algb,
                         "achieved_gbs": (algb / 1e9) / (avg_ms / 1e3) if avg_ms > 0 else 0.0})
     top = kernels[0]
+    traffic, traffic_src = measured_traffic(top["kernel"])
     roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peak,
-                "unit": "GB/s", "frac": top["achieved_gbs"] / peak, "traffic": None,
+                "unit": "GB/s", "frac": top["achieved_gbs"] / peak, "traffic": traffic,
+                "traffic_source": traffic_src,
                 "peak_source": peak_src, "avg_launch_ms": top["avg_ms"],
                 "share_of_step": top["share"],
                 "alg_bytes_per_launch": top["alg_bytes_per_launch"],
@@ -315,7 +328,7 @@ def run_ours(args):
                        "stream sync every step", "reward_checksum": checksum},
         "gpu_launches": sim.last_step_launches() * args.steps,
         "launches_per_step": sim.last_step_launches(),
-        "clocks": clocks, "roofline": roofline, "kernels": kernels[:8],
+        "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "overflow": sim.overflow_count(),
     }
     if cpu_baseline:

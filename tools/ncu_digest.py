@@ -33,3 +33,16 @@ for r in rows[2:]:
         except ValueError:
             vals.append(r[i])
     print('| ' + r[ki].split('(')[0] + ' | ' + ' | '.join(vals) + ' |')
+
+if len(sys.argv) > 3 and sys.argv[2] == '--traffic':
+    # profiles/traffic.json: mean DRAM bytes per launch and kernel, scaled to a whole-shard launch
+    import collections, json
+    scale = float(sys.argv[4]) if len(sys.argv) > 4 else 1.0
+    ir, iw = hdr.index('dram__bytes_read.sum'), hdr.index('dram__bytes_write.sum')
+    mult = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    acc = collections.defaultdict(list)
+    for r in rows[2:]:
+        name = r[ki].split('(')[0].replace('void ', '').split('<')[0].replace('hs::', '')
+        acc[name].append(float(r[ir].replace(',', '')) * mult[units[ir]] + float(r[iw].replace(',', '')) * mult[units[iw]])
+    out = {'source': sys.argv[3], 'kernels': {k: scale * sum(v) / len(v) for k, v in acc.items()}}
+    json.dump(out, open('profiles/traffic.json', 'w'), indent=1)
