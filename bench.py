@@ -112,8 +112,8 @@ def kernel_alg_bytes(name, A, E, C, K):
         "k_rewards": A * (pose + 8),
         "k_reset": 4,
         "k_observations": A * (13 + 70 + 153 + 28) * 4 + E * posevel,
-        "k_visibility": A * 16 * 4 + E * pose,
-        "k_lidar": A * 120 + E * (40 + 4),
+        # leaf records in (40 B + meta), 30 lidar floats + 16 visibility flags x4 B out
+        "k_rays": A * (120 + 64) + E * (40 + 4),
         "k_debug_positions": 136 + 17 * 8,
     }
     return float(table.get(name, 0))
@@ -320,7 +320,7 @@ def run_ours(args):
         "config": {"workload": "scripts/benchmark.py semantics: 16000 worlds/GPU x steps, 2 hiders + 2 "
                                "seekers, random move actions every step, renderer off",
                    "worlds_per_gpu": N, "agents_per_world": A, "sharding": f"worlds x{world}",
-                   "l2": "per-GPU state (BVH 208 MB + bodies 140 MB + exports 81 MB) exceeds the 126 MB L2",
+                   "l2": "per-GPU state (BVH 208 MB + body records 186 MB + contacts 328 MB + exports 81 MB) exceeds the 126 MB L2",
                    "mean_bodies": E, "mean_candidates": C, "mean_contacts": K},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": R * 5 * 4,
                 "d2h_bytes_per_step": R * 8, "steps": e2e_steps,

@@ -1,4 +1,4 @@
-for cfg in "1 1" "2 2" "4 1" "8 1" "8 2" "16 2" "16 4" "32 2" "32 4"; do
+for cfg in "1 1" "2 2" "3 3" "4 4" "4 2"; do
   set -- $cfg
   HIDESEEK_STEP_SLICES=$1 HIDESEEK_STEP_BRANCHES=$2 python bench.py --steps 240 --warmup 5 --no-cpu-baseline --profile-steps 1 > gpurun_out/sweep.json
   python -c "
