@@ -41,6 +41,24 @@ def parse_args():
     return ap.parse_args()
 
 
+_JSON_OUT = None
+
+
+def guard_stdout():
+    """Keep stdout for the ONE JSON line: libraries that print to fd 1 (NCCL's version banner,
+    the reference backend's log lines) are sent to stderr instead."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def measured_peak_gbs():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -160,9 +178,9 @@ def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    # bounded sample of the same workload: fewer worlds (the CPU backend runs one world
-    # per job, so throughput is flat in world count once worlds >> cores)
-    worlds = 2000
+    # the full 16000-world shard when the step budget allows, else fewer worlds (the CPU
+    # backend runs one world per job, so throughput is flat in world count once worlds >> cores)
+    worlds = args.worlds
     steps, warmup = max(1, args.steps), max(0, args.warmup)
     t0 = time.time()
     # keep the whole run within a few minutes: scale the per-call step count down
@@ -186,7 +204,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": time.time() - t0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -306,7 +324,10 @@ def run_ours(args):
 
     cpu_baseline = None
     if not args.no_cpu_baseline and world == 1:
-        cw, cs = 1024, 24
+        # same shard size; step count chosen for ~12 s of CPU work from a 2-step probe
+        cw = N
+        _, probe_secs, _ = cpu_reference_run(cw, 1, 2, 0)
+        cs = int(min(96, max(8, 12.0 / max(probe_secs / 2, 1e-3))))
         v, secs, cores = cpu_reference_run(cw, 2, cs, 0)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference",
                         "sample": f"{cw} worlds x {cs} steps ({secs:.1f} s), all host threads, "
@@ -333,13 +354,14 @@ def run_ours(args):
     }
     if cpu_baseline:
         line["cpu_baseline"] = cpu_baseline
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a = parse_args()
+    guard_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
