@@ -99,12 +99,16 @@ EXPORTS = [("seed", "seed", "int"), ("self_type", "self_type", "int"), ("self_ma
            ("episode_result", "episode_result", "world"), ("global_positions", "global_pos", "globalpos")]
 
 
-def compare_exports(sim, rt, min_agents, tol, skip=()):
+def compare_exports(sim, rt, min_agents, tol, skip=(), prev_active=None):
     """Compare every exported tensor.  Rows of inactive agent interfaces hold
     uninitialised memory in the reference and are skipped.
+    Reward / done are written BEFORE the reset stage of a step (src/sim.cpp:805-842 runs ahead
+    of resetSystem), so a row whose agent only appeared in this step's reset still holds
+    uninitialised reward / done: pass the activity mask from before the step as `prev_active`.
     Returns (errors, max float difference)."""
     errs, maxd = [], 0.0
     active = rt["self_mask"].reshape(-1) == 1.0
+    written = active if prev_active is None else (active & prev_active)
     for name, key, kind in EXPORTS:
         if name in skip:
             continue
@@ -118,7 +122,8 @@ def compare_exports(sim, rt, min_agents, tol, skip=()):
             k = 11 + min_agents
             mine, theirs = mine[:, :k], theirs[:, :k]
         elif kind != "world":
-            mine, theirs = mine[active], theirs[active]
+            rows = written if name in ("reward", "done") else active
+            mine, theirs = mine[rows], theirs[rows]
         if kind == "int":
             if not np.array_equal(mine, theirs):
                 errs.append(name)

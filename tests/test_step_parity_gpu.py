@@ -18,7 +18,8 @@ pytestmark = pytest.mark.gpu
 POS_TOL = 1e-4      # abs, positions / quaternions / velocities / lidar depth, per step
 
 
-def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, check_every=1):
+def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, check_every=1,
+              reset_prob=0.0):
     import gpu_hideseek as gh
     ref = refsim.RefSim(N, sim_flags=flags, seed=seed, min_hiders=hs[0], max_hiders=hs[1],
                         min_seekers=sk[0], max_seekers=sk[1], num_threads=1)
@@ -28,6 +29,7 @@ def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, 
     sim.init()
     rt = ref.tensors()
     act = sim.action_tensor().to_torch()
+    rst = sim.reset_tensor().to_torch()
     import torch
     rng = np.random.RandomState(1234 + seed)
     A = hs[1] + sk[1]
@@ -43,7 +45,13 @@ def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, 
             a[:, 3] = rng.rand(N * A) < 0.3
             a[:, 4] = rng.rand(N * A) < 0.15
         rt["action"][:] = a
+        if reset_prob > 0.0:
+            # scripts/benchmark.py:77-80 (reset_chance): level-1 resets in the middle of episodes
+            r = (rng.rand(N, 1) < reset_prob).astype(np.int32)
+            rt["reset"][:] = r
+            rst.copy_(torch.from_numpy(r).to(rst.device))
         act.copy_(torch.from_numpy(a).to(act.device))
+        prev_active = rt["self_mask"].reshape(-1) == 1.0
         ref.step()
         sim.step()
         if step % check_every and step != steps - 1:
@@ -64,7 +72,7 @@ def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, 
             nb = int(rw["num_bodies"])
             for f in ("pos", "rot", "vel"):
                 maxdiff = max(maxdiff, float(np.abs(rw["bodies"][f][:nb] - hw["bodies"][f][:nb]).max()))
-        errs, d = compare_exports(sim, rt, hs[0] + sk[0], tol=5e-4)
+        errs, d = compare_exports(sim, rt, hs[0] + sk[0], tol=5e-4, prev_active=prev_active)
         assert not errs, (step, errs)
         maxdiff = max(maxdiff, d)
     print(f"max abs difference over {steps} steps: {maxdiff:g}")
@@ -89,3 +97,10 @@ def test_zero_vel_fixed_world_flip_teams():
 def test_episode_rollover_resets():
     # crosses step 239 -> automatic reset -> second episode level must be bit-exact again
     _run_pair(8, seed=3, flags=0, steps=245, hs=(1, 3), sk=(1, 3), check_every=40)
+
+
+def test_reset_heavy():
+    # a random quarter of the worlds is reset every step, so episodes
+    # of every age coexist and the entity-id LIFO / BVH rebuild run on every step
+    _run_pair(24, seed=7, flags=0, steps=60, hs=(1, 3), sk=(1, 3), use_grab_lock=True,
+              check_every=6, reset_prob=0.25)

@@ -1,2 +1,11 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -6; python bench.py --steps 240 --warmup 5 --no-cpu-baseline > gpurun_out/cur_bench.json; python -c "
-import json; d=json.load(open('gpurun_out/cur_bench.json')); print(d['ms_per_step'], d['value'], 'e2e', d['e2e']['value']); [print(k['kernel'], round(k['avg_ms'],4), k['launches_per_step']) for k in d['kernels']]"
+#!/bin/bash
+# pytest -m gpu, then a 240-step bench with the per-kernel table
+python -m pytest tests -x -q -m gpu 2>&1 | tail -5
+python bench.py --steps 240 --warmup 5 --no-cpu-baseline --profile-steps 8 > gpurun_out/tb.json 2> gpurun_out/tb.err || tail -5 gpurun_out/tb.err
+python - <<'PY'
+import json
+d = json.load(open('gpurun_out/tb.json'))
+print('ms/step', round(d['ms_per_step'], 4), 'value', round(d['value']), 'e2e', round(d['e2e']['value']))
+for k in d.get('kernels', [])[:12]:
+    print(k)
+PY
