@@ -37,6 +37,13 @@ __device__ __forceinline__ Quat angleAxisZ(float angle)
     return {c, 0.f * s, 0.f * s, 1.f * s};
 }
 
+__device__ __forceinline__ Quat angleAxis(float angle, Vec3 n)
+{
+    float s, c;
+    hs_det_sincosf(angle / 2.f, &s, &c);
+    return {c, n.x * s, n.y * s, n.z * s};
+}
+
 struct WallSet {
     static constexpr int kCap = 36;
     float p1x[kCap], p1y[kCap], p2x[kCap], p2y[kCap];
@@ -433,6 +440,113 @@ __device__ inline void generateTrainingWorld(const DeviceState &S, int w, Rng &e
     WI(S, WF_NUM_RAMPS, w) = kMaxRamps;
 }
 
+// generateDebugEnvironment (src/level_gen.cpp:336-526): the fixed physics fixtures behind
+// triggerReset(world, 2..8).  Every level lists its DynamicObject rows first and its agents
+// after them, so slots and BVH leaves are both handed out in creation order.  Boxes / ramps are
+// NOT registered with the observation lists (numActiveBoxes / numActiveRamps stay 0).
+// Level 5 never records its plane in obstacles[] (level_gen.cpp:396-405), so in the reference
+// that plane survives the world's next reset as an orphan row; here it is torn down with the
+// rest of the world, i.e. parity for a level-5 world holds until its next reset.
+struct DebugWorld {
+    const DeviceState &S;
+    int w;
+    IdPool &ids;
+    int slot = 0, leaf = 0, nAgents = 0, nh = 0, nsk = 0;
+
+    __device__ int object(Vec3 pos, Quat rot, int obj, int resp = RESP_DYNAMIC, int owner = OWNER_NONE,
+                          Vec3 scale = {1.f, 1.f, 1.f})
+    {
+        NewBody b{pos, rot, scale, obj, resp, owner};
+        writeBody(S, w, slot, b, ids.acquire(), leaf++);
+        return slot++;
+    }
+    __device__ int plane(Vec3 pos, Quat rot) { return object(pos, rot, OBJ_PLANE, RESP_STATIC, OWNER_UNOWNABLE); }
+    // makeAgent (level_gen.cpp:12-66); only called once every object row exists
+    __device__ void agent(Vec3 pos, Quat rot, bool seeker)
+    {
+        const int A = S.p.agentsPerWorld;
+        if (nAgents >= A) return;
+        NewBody b{pos, rot, {1.f, 1.f, 1.f}, seeker ? OBJ_SEEKER : OBJ_HIDER, RESP_DYNAMIC, OWNER_UNOWNABLE};
+        int k = nAgents++;
+        int aslot = slot + k;
+        writeBody(S, w, aslot, b, ids.acquire(), leaf++);
+        JMETA(S, k, w) = 0xFFFFFFFFu;
+        WB(S, WB_IFACE_SLOT + k, w) = (uint8_t)aslot;
+        WB(S, WB_IFACE_TYPE + k, w) = seeker ? AGENT_SEEKER : AGENT_HIDER;
+        if (seeker) WB(S, WB_SEEKER_SLOT + nsk++, w) = (uint8_t)aslot;
+        else WB(S, WB_HIDER_SLOT + nh++, w) = (uint8_t)aslot;
+        size_t row = size_t(w) * A + k;
+        S.exSelfType[row] = seeker ? AGENT_SEEKER : AGENT_HIDER;
+        S.exSelfMask[row] = 1.f;
+        S.exSeed[row * 2 + 0] = WI(S, WF_EP_KEY_A, w);
+        S.exSeed[row * 2 + 1] = WI(S, WF_EP_KEY_B, w);
+        int32_t *act = S.exAction + row * 5;
+        act[0] = 2; act[1] = 2; act[2] = 2; act[3] = 0; act[4] = 0;
+    }
+};
+
+__device__ inline void generateDebugWorld(const DeviceState &S, int w, int level, IdPool &ids)
+{
+    constexpr float kPi = 3.14159265358979323846264338327950288f;
+    constexpr float kPiD2 = kPi / 2.f;
+    constexpr float kDeg = kPi / 180.f;            // toRadians (math.inl:7-11)
+    const Vec3 X = {1.f, 0.f, 0.f}, Y = {0.f, 1.f, 0.f}, Z = {0.f, 0.f, 1.f};
+    const Quat flat = angleAxis(0.f, X);
+    DebugWorld D{S, w, ids};
+    switch (level) {
+    case 2: {   // cube balanced on a corner; atanf(1/sqrtf(2)) as glibc rounds it (0x3f1d9014)
+        Quat r = qnormalize(qnormalize(angleAxis(__int_as_float(0x3f1d9014), Y) * angleAxis(kDeg * 45.f, X)));
+        D.object({0.f, 0.f, 5.f}, r, OBJ_CUBE);
+        D.plane({0.f, 0.f, 0.f}, flat);
+    } break;
+    case 3:
+        D.object({0.f, 0.f, 5.f}, angleAxis(0.f, Z), OBJ_CUBE);
+        D.plane({0.f, 0.f, 0.f}, flat);
+        break;
+    case 4:
+        D.object(v3(0.f, 0.f, 5.f) + v3(0.f, 0.f, 5.f), qnormalize(angleAxis(kDeg * 45.f, Y)), OBJ_BOX);
+        D.plane({0.f, 0.f, 0.f}, flat);
+        break;
+    case 5:
+        D.plane({0.f, 0.f, 0.f}, flat);
+        D.agent({0.f, 0.f, 1.f}, Quat{1.f, 0.f, 0.f, 0.f}, false);
+        break;
+    case 6:
+        D.plane({0.f, 0.f, 0.f}, flat);
+        D.object({0.f, 0.f, 0.f}, flat, OBJ_WALL, RESP_STATIC, OWNER_UNOWNABLE, {10.f, 0.2f, 1.f});
+        D.object({0.f, -5.f, 1.f}, flat, OBJ_CUBE);
+        D.agent({-15.f, -15.f, 1.5f}, angleAxis(kDeg * -45.f, Z), false);
+        D.agent({-15.f, -10.f, 1.5f}, angleAxis(kDeg * 45.f, Z), true);
+        break;
+    case 7: {
+        Quat r = qnormalize(angleAxis(kDeg * 45.f, Y) * angleAxis(kDeg * 40.f, X));
+        D.object({0.f, 0.f, 5.f}, r, OBJ_CUBE);
+        D.object(v3(0.f, 0.f, 5.f) + v3(0.f, 0.f, 5.f), r, OBJ_CUBE);
+        D.plane({0.f, 0.f, 0.f}, flat);
+        D.plane({-20.f, 0.f, 0.f}, angleAxis(kPiD2, Y));
+        D.plane({20.f, 0.f, 0.f}, angleAxis(-kPiD2, Y));
+    } break;
+    case 8: {
+        Quat r = qnormalize(angleAxis(kDeg * 25.f, Y) * angleAxis(kDeg * 90.f, Z) * angleAxis(kDeg * 45.f, X));
+        int ramp = D.object({0.f, 0.f, 10.f}, r, OBJ_RAMP);
+        BF(S, BF_VZ, ramp, w) = -30.f;
+        D.object({-0.5f, -0.5f, 1.f}, qnormalize(angleAxis(kDeg * -90.f, X) * angleAxis(kPi, Y)), OBJ_RAMP,
+                 RESP_STATIC, OWNER_NONE);
+        D.plane({0.f, 0.f, 0.f}, flat);
+        D.plane({-20.f, 0.f, 0.f}, angleAxis(kPiD2, Y));
+        D.plane({20.f, 0.f, 0.f}, angleAxis(-kPiD2, Y));
+    } break;
+    default: break;     // unknown level ids generate an empty world, as in the reference
+    }
+    WI(S, WF_NUM_DYN, w) = D.slot;
+    WI(S, WF_NUM_BODIES, w) = D.slot + D.nAgents;
+    WI(S, WF_NUM_AGENTS, w) = D.nAgents;
+    WI(S, WF_NUM_HIDERS, w) = D.nh;
+    WI(S, WF_NUM_SEEKERS, w) = D.nsk;
+    WI(S, WF_NUM_BOXES, w) = 0;
+    WI(S, WF_NUM_RAMPS, w) = 0;
+}
+
 // resetEnvironment + generateEnvironment for one world.  `ckpt == nullptr`: the episode
 // reset of resetSystem (new episode key, agent counts drawn from the episode RNG).
 // `ckpt != nullptr`: the regeneration half of loadCheckpointSystem (src/sim.cpp:966-985):
@@ -440,7 +554,7 @@ __device__ inline void generateTrainingWorld(const DeviceState &S, int w, Rng &e
 // agent-count draws are burned and the saved counts are used instead.
 struct CkptRegen { RandKey key; int numHiders, numSeekers; };
 
-__device__ inline void regenerateWorld(const DeviceState &S, int w, const CkptRegen *ckpt)
+__device__ inline void regenerateWorld(const DeviceState &S, int w, const CkptRegen *ckpt, int level = 1)
 {
     IdPool ids(S, w);
     WI(S, WF_EPISODE_STEP, w) = 0;
@@ -468,7 +582,8 @@ __device__ inline void regenerateWorld(const DeviceState &S, int w, const CkptRe
     RandKey lvlKey = rng.advance();        // levelGenRandKey always draws
     if (S.p.simFlags & FLAG_FIXED_WORLD) lvlKey = {0, 0};
 
-    generateTrainingWorld(S, w, rng, lvlKey, numHiders, numSeekers, ids);
+    if (level == 1) generateTrainingWorld(S, w, rng, lvlKey, numHiders, numSeekers, ids);
+    else generateDebugWorld(S, w, level, ids);
 
     // generateEnvironment tail (level_gen.cpp:326-333): park unused interfaces
     int nAgents = WI(S, WF_NUM_AGENTS, w);
@@ -497,7 +612,7 @@ __global__ void k_reset(DeviceState S)
 
     if (level != 0) {
         S.exReset[w] = 0;
-        regenerateWorld(S, w, nullptr);
+        regenerateWorld(S, w, nullptr, level);
     } else {
         WI(S, WF_EPISODE_STEP, w) = step + 1;
         WI(S, WF_DID_RESET, w) = 0;

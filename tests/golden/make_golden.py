@@ -6,7 +6,7 @@ under /root/reference by oracle/Makefile) single-threaded on fixed seeds and a f
 tape, and stores per-world internal state + every exported tensor after init and after
 selected steps.  The fixtures travel with the repo; the GPU box has no /root/reference.
 
-    python tests/golden/make_golden.py          # rewrites tests/golden/*.npz
+    python tests/golden/make_golden.py [case ...]   # rewrites tests/golden/<case>.npz (default: all)
 """
 import os
 import sys
@@ -22,7 +22,11 @@ CASES = [
     ("bench_seed0", 4, 0, 0, (2, 2), (2, 2), 12, (0, 1, 6, 12), False),
     ("ragged_seed5_grablock", 4, 5, 0, (1, 3), (1, 3), 110, (0, 100, 110), True),
     ("train_flags_seed5", 3, 5, 1 | 4 | 8, (3, 3), (3, 3), 104, (0, 104), True),
+    ("debug_levels", 8, 2, 0, (1, 2), (1, 2), 90, (0, 3, 45, 90), True),
 ]
+
+# triggerReset(world, level) issued before step 1 (src/level_gen.cpp:336-526 fixtures)
+LEVELS = {"debug_levels": [2, 3, 4, 5, 6, 7, 8, 1]}
 
 EXPORT_KEYS = ["prep_counter", "action", "self_obs", "self_type", "self_mask", "agent_obs", "box_obs",
                "ramp_obs", "agent_vis", "box_vis", "ramp_vis", "lidar", "seed", "reward", "done",
@@ -49,7 +53,10 @@ def snapshot(ref, N):
 
 
 def main():
+    only = set(sys.argv[1:])
     for name, N, seed, flags, hs, sk, steps, snaps, grab_lock in CASES:
+        if only and name not in only:
+            continue
         ref = refsim.RefSim(N, sim_flags=flags, seed=seed, min_hiders=hs[0], max_hiders=hs[1],
                             min_seekers=sk[0], max_seekers=sk[1], num_threads=1)
         ref.init()
@@ -57,6 +64,9 @@ def main():
         tape = action_tape(name, steps, N * A, bool(flags & 8), grab_lock)
         data = {"config": np.array([N, seed, flags, hs[0], hs[1], sk[0], sk[1], steps], dtype=np.int64),
                 "snaps": np.array(snaps, dtype=np.int64), "tape": tape.astype(np.int8)}
+        levels = LEVELS.get(name)
+        if levels is not None:
+            data["levels"] = np.array(levels, dtype=np.int64)
         rt = ref.tensors()
         for s in range(steps + 1):
             if s in snaps:
@@ -64,6 +74,9 @@ def main():
                     data[f"s{s}_{k}"] = v
             if s < steps:
                 rt["action"][:] = tape[s]
+                if s == 1 and levels is not None:
+                    for w, lvl in enumerate(levels):
+                        ref.trigger_reset(w, lvl)
                 ref.step()
         ref.close()
         path = os.path.join(HERE, name + ".npz")

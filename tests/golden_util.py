@@ -24,6 +24,8 @@ class Golden:
         self.A = self.max_h + self.max_s
         self.snaps = [int(x) for x in d["snaps"]]
         self.tape = d["tape"].astype(np.int32)
+        # optional: level ids passed to triggerReset(world, level) before step 1
+        self.levels = [int(x) for x in d["levels"]] if "levels" in d.files else None
 
     def worlds(self, step):
         return self.d[f"s{step}_worlds"]

@@ -11,7 +11,7 @@ FLOAT_TOL = 1e-6     # libm atan2f/asinf in the observation euler angles may dif
 
 
 def test_fixtures_present():
-    assert len(case_names()) >= 3
+    assert len(case_names()) >= 4
 
 
 @pytest.mark.parametrize("name", case_names())
@@ -52,5 +52,8 @@ def test_oracle_reproduces_golden(name):
                     assert np.abs(a.astype(np.float64) - b).max(initial=0.0) <= FLOAT_TOL, (s, k)
         if s < g.steps:
             rt["action"][:] = g.tape[s]
+            if s == 1 and g.levels is not None:
+                for w, lvl in enumerate(g.levels):
+                    ref.trigger_reset(w, lvl)
             ref.step()
     ref.close()

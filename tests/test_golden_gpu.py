@@ -35,6 +35,9 @@ def test_cuda_matches_golden(name):
             maxd = max(maxd, d)
         if s < g.steps:
             act.copy_(torch.from_numpy(g.tape[s]).to(act.device))
+            if s == 1 and g.levels is not None:
+                for w, lvl in enumerate(g.levels):
+                    sim.trigger_reset(w, lvl)
             sim.step()
     assert sim.overflow_count() == 0
     print(f"{name}: max |export diff| vs golden = {maxd:g}")

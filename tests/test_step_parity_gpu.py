@@ -19,7 +19,7 @@ POS_TOL = 1e-4      # abs, positions / quaternions / velocities / lidar depth, p
 
 
 def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, check_every=1,
-              reset_prob=0.0):
+              reset_prob=0.0, levels=None, min_agents=None):
     import gpu_hideseek as gh
     ref = refsim.RefSim(N, sim_flags=flags, seed=seed, min_hiders=hs[0], max_hiders=hs[1],
                         min_seekers=sk[0], max_seekers=sk[1], num_threads=1)
@@ -45,6 +45,11 @@ def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, 
             a[:, 3] = rng.rand(N * A) < 0.3
             a[:, 4] = rng.rand(N * A) < 0.15
         rt["action"][:] = a
+        if levels is not None and step == 1:
+            # triggerReset(world, level): the debug fixtures of src/level_gen.cpp:336-526
+            for w_, lvl in enumerate(levels):
+                ref.trigger_reset(w_, lvl)
+                sim.trigger_reset(w_, lvl)
         if reset_prob > 0.0:
             # scripts/benchmark.py:77-80 (reset_chance): level-1 resets in the middle of episodes
             r = (rng.rand(N, 1) < reset_prob).astype(np.int32)
@@ -72,7 +77,8 @@ def _run_pair(N, seed, flags, steps, hs=(2, 2), sk=(2, 2), use_grab_lock=False, 
             nb = int(rw["num_bodies"])
             for f in ("pos", "rot", "vel"):
                 maxdiff = max(maxdiff, float(np.abs(rw["bodies"][f][:nb] - hw["bodies"][f][:nb]).max()))
-        errs, d = compare_exports(sim, rt, hs[0] + sk[0], tol=5e-4, prev_active=prev_active)
+        errs, d = compare_exports(sim, rt, hs[0] + sk[0] if min_agents is None else min_agents, tol=5e-4,
+                                  prev_active=prev_active)
         assert not errs, (step, errs)
         maxdiff = max(maxdiff, d)
     print(f"max abs difference over {steps} steps: {maxdiff:g}")
@@ -104,3 +110,12 @@ def test_reset_heavy():
     # of every age coexist and the entity-id LIFO / BVH rebuild run on every step
     _run_pair(24, seed=7, flags=0, steps=60, hs=(1, 3), sk=(1, 3), use_grab_lock=True,
               check_every=6, reset_prob=0.25)
+
+
+def test_debug_levels_2_to_8():
+    # falling cube / box / ramp fixtures, the single-agent and the
+    # wall + cube + two-agent levels, next to one ordinary training world (level 1).
+    # 150 steps: long enough for every body to land, bounce and settle, short of the
+    # episode rollover (level 5 leaks its plane across a reset in the reference).
+    _run_pair(8, seed=2, flags=0, steps=150, hs=(2, 2), sk=(2, 2), use_grab_lock=True, check_every=5,
+              levels=[2, 3, 4, 5, 6, 7, 8, 1], min_agents=0)
