@@ -17,6 +17,7 @@
 #ifndef HIDESEEK_C_API_H
 #define HIDESEEK_C_API_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -91,6 +92,31 @@ int hs_save_checkpoint(hs_sim *sim, int world);
 int hs_load_checkpoint(hs_sim *sim, int world);
 int hs_save_checkpoints(hs_sim *sim, void *stream);
 int hs_load_checkpoints(hs_sim *sim, void *stream);
+
+/* The JAX / XLA path (Manager::gpuJAXInit / gpuJAXStep / gpuJAXSaveCheckpoints /
+ * gpuJAXLoadCheckpoints, src/mgr.cpp:365-437, 987-1060).  `buffers` is the flat list of DEVICE
+ * pointers of an XLA GPU custom call after the two entries Madrona's wrapper skips:
+ *   init:  out 11 observations in JAXIOObservations order (src/mgr.cpp:168-201):
+ *          prep_counter, self_data, self_type, self_mask, lidar, agent_data, box_data,
+ *          ramp_data, vis_agents_mask, vis_boxes_mask, vis_ramps_mask      (waits for the stream)
+ *   step:  in actions, resets, policy_assignments; out 11 observations, rewards, dones,
+ *          episode_results                                                  (fully asynchronous)
+ *   save:  in checkpoint_control; out checkpoint_data
+ *   load:  in checkpoint_control, checkpoint_data; out 11 observations
+ * Copies are device-to-device on `stream`; shapes/dtypes are those of hs_export. */
+int hs_jax_init(hs_sim *sim, void *stream, void **buffers);
+int hs_jax_step(hs_sim *sim, void *stream, void **buffers);
+int hs_jax_save_checkpoints(hs_sim *sim, void *stream, void **buffers);
+int hs_jax_load_checkpoints(hs_sim *sim, void *stream, void **buffers);
+
+/* The entry points an XLA GPU custom-call registration is given (JAXInterface::gpuEntryFn,
+ * external/madrona/include/madrona/py/bindings.inl:107-119): `opaque` carries the hs_sim*,
+ * buffers[0] is the CPU-backend slot and buffers[1] JAX's ordering token (both skipped).
+ * They abort on failure, as the reference's REQ_CUDA does. */
+void hs_xla_gpu_init(void *stream, void **buffers, const char *opaque, size_t opaque_len);
+void hs_xla_gpu_step(void *stream, void **buffers, const char *opaque, size_t opaque_len);
+void hs_xla_gpu_save_checkpoints(void *stream, void **buffers, const char *opaque, size_t opaque_len);
+void hs_xla_gpu_load_checkpoints(void *stream, void **buffers, const char *opaque, size_t opaque_len);
 
 /* Diagnostics / parity: flat per-world internal state (layout in
  * hideseek/debug_dump.h), number of kernels launched by the last hs_step,

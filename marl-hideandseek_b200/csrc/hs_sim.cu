@@ -529,6 +529,116 @@ extern "C" int hs_load_checkpoints(hs_sim *sim, void *stream)
     return 0;
 }
 
+// ---- XLA / JAX buffer contract (src/mgr.cpp:168-201, 326-437) ----------------------------------
+// `buffers` is the flat device-pointer list an XLA GPU custom call receives, AFTER the two leading
+// entries the Madrona wrapper skips (M/include/madrona/py/bindings.inl:107-119).  Everything is
+// enqueued on the caller's stream; only hs_jax_init waits (the reference synchronises there).
+static size_t exportBytes(hs_sim *sim, int id, void **ptr)
+{
+    int dt, nd; int64_t dims[4];
+    if (hs_export(sim, id, ptr, &dt, &nd, dims)) return 0;
+    size_t n = dt == HS_U8 ? 1 : 4;
+    for (int i = 0; i < nd; i++) n *= size_t(dims[i]);
+    return n;
+}
+
+static int copyOut(hs_sim *sim, cudaStream_t st, int id, void *dst)
+{
+    void *src; size_t n = exportBytes(sim, id, &src);
+    HS_CUDA(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+static int copyIn(hs_sim *sim, cudaStream_t st, int id, const void *src)
+{
+    void *dst; size_t n = exportBytes(sim, id, &dst);
+    HS_CUDA(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+// JAXIOObservations::set order (src/mgr.cpp:168-201)
+static const int kJaxObsOrder[11] = {
+    HS_EXPORT_PREP_COUNTER, HS_EXPORT_SELF_OBS, HS_EXPORT_SELF_TYPE, HS_EXPORT_SELF_MASK, HS_EXPORT_LIDAR,
+    HS_EXPORT_AGENT_OBS, HS_EXPORT_BOX_OBS, HS_EXPORT_RAMP_OBS,
+    HS_EXPORT_AGENT_VIS, HS_EXPORT_BOX_VIS, HS_EXPORT_RAMP_VIS,
+};
+
+static int copyOutObservations(hs_sim *sim, cudaStream_t st, void **&buffers)
+{
+    for (int i = 0; i < 11; i++)
+        if (copyOut(sim, st, kJaxObsOrder[i], *buffers++)) return 1;
+    return 0;
+}
+
+extern "C" int hs_jax_init(hs_sim *sim, void *stream, void **buffers)
+{
+    if (!sim || !buffers) { g_err = "hs_jax_init: null argument"; return 1; }
+    if (hs_init(sim, stream)) return 1;
+    if (copyOutObservations(sim, (cudaStream_t)stream, buffers)) return 1;
+    HS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int hs_jax_step(hs_sim *sim, void *stream, void **buffers)
+{
+    if (!sim || !buffers) { g_err = "hs_jax_step: null argument"; return 1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    if (copyIn(sim, st, HS_EXPORT_ACTION, *buffers++)) return 1;
+    if (copyIn(sim, st, HS_EXPORT_RESET, *buffers++)) return 1;
+    if (copyIn(sim, st, HS_EXPORT_AGENT_POLICY, *buffers++)) return 1;
+    if (hs_step(sim, stream)) return 1;
+    if (copyOutObservations(sim, st, buffers)) return 1;
+    if (copyOut(sim, st, HS_EXPORT_REWARD, *buffers++)) return 1;
+    if (copyOut(sim, st, HS_EXPORT_DONE, *buffers++)) return 1;
+    if (copyOut(sim, st, HS_EXPORT_EPISODE_RESULT, *buffers++)) return 1;
+    return 0;
+}
+
+extern "C" int hs_jax_save_checkpoints(hs_sim *sim, void *stream, void **buffers)
+{
+    if (!sim || !buffers) { g_err = "hs_jax_save_checkpoints: null argument"; return 1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    if (copyIn(sim, st, HS_EXPORT_CKPT_CTRL, buffers[0])) return 1;
+    if (hs_save_checkpoints(sim, stream)) return 1;
+    return copyOut(sim, st, HS_EXPORT_CKPT, buffers[1]);
+}
+
+extern "C" int hs_jax_load_checkpoints(hs_sim *sim, void *stream, void **buffers)
+{
+    if (!sim || !buffers) { g_err = "hs_jax_load_checkpoints: null argument"; return 1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    if (copyIn(sim, st, HS_EXPORT_CKPT_CTRL, *buffers++)) return 1;
+    if (copyIn(sim, st, HS_EXPORT_CKPT, *buffers++)) return 1;
+    if (hs_load_checkpoints(sim, stream)) return 1;
+    return copyOutObservations(sim, st, buffers);
+}
+
+// The functions XLA itself would be handed (gpuEntryFn, bindings.inl:107-119): `opaque` holds the
+// simulator pointer, buffers[0] is the CPU-backend slot and buffers[1] JAX's ordering token.
+// XLA custom calls cannot return a status, so a failure aborts like the reference's REQ_CUDA.
+static hs_sim *xlaSim(const char *opaque, size_t len, const char *who)
+{
+    hs_sim *sim = nullptr;
+    if (opaque && len >= sizeof(hs_sim *)) memcpy(&sim, opaque, sizeof(hs_sim *));
+    if (!sim) { fprintf(stderr, "%s: opaque does not hold a simulator pointer\n", who); abort(); }
+    return sim;
+}
+#define HS_XLA_ENTRY(name, call)                                                                   \
+    extern "C" void name(void *stream, void **buffers, const char *opaque, size_t opaque_len)     \
+    {                                                                                              \
+        if (call(xlaSim(opaque, opaque_len, #name), stream, buffers + 2)) {                        \
+            fprintf(stderr, #name ": %s\n", g_err.c_str());                                        \
+            abort();                                                                               \
+        }                                                                                          \
+    }
+HS_XLA_ENTRY(hs_xla_gpu_init, hs_jax_init)
+HS_XLA_ENTRY(hs_xla_gpu_step, hs_jax_step)
+HS_XLA_ENTRY(hs_xla_gpu_save_checkpoints, hs_jax_save_checkpoints)
+HS_XLA_ENTRY(hs_xla_gpu_load_checkpoints, hs_jax_load_checkpoints)
+
 static int setCkptTrigger(hs_sim *sim, int world, const char *who)
 {
     if (!sim || world < 0 || world >= sim->cfg.num_worlds) { g_err = std::string(who) + ": bad world"; return 1; }

@@ -132,6 +132,19 @@ class HideAndSeekSimulator(_native.HideAndSeekSimulator):
         n = float(self.num_worlds)
         return dict(bodies=out[0] / n, agents=out[1] / n, candidates=out[2] / n, contacts=out[3] / n)
 
+    def xla_custom_calls(self):
+        """What an XLA GPU custom-call registration needs (M/src/python/jax_register.py): the
+        addresses of the four entry points `void fn(cudaStream_t, void **buffers, const char
+        *opaque, size_t opaque_len)` in libhideseek_b200.so and the `opaque` bytes (this
+        simulator's pointer).  Buffers 0 and 1 of a call are the CPU slot and JAX's token."""
+        import struct
+        fns = {}
+        for key, sym in (("init", "hs_xla_gpu_init"), ("step", "hs_xla_gpu_step"),
+                         ("save_ckpts", "hs_xla_gpu_save_checkpoints"),
+                         ("restore_ckpts", "hs_xla_gpu_load_checkpoints")):
+            fns[key] = C.cast(getattr(self._clib, sym), C.c_void_p).value
+        return dict(fns=fns, opaque=struct.pack("P", self.handle()))
+
     def last_step_launches(self):
         return self._clib.hs_last_step_launches(self._h)
 

@@ -6,6 +6,7 @@
 // (M/src/python/bindings.cpp:52-68): no owner, the pointer stays valid for the lifetime of
 // the simulator object, which the returned Python tensor keeps alive.
 #include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
 
 #include <cstring>
 #include <stdexcept>
@@ -212,6 +213,40 @@ PYBIND11_MODULE(_native, m)
             throw std::runtime_error("jax interface: jax / XLA are not installed in this environment "
                                      "(SURVEY.md §8f-1; use the DLPack tensors with PyTorch)");
         })
+        // TrainInterface (src/mgr.cpp:1338-1375) as nested dicts of named tensors, in the
+        // reference's order (Python dicts keep insertion order)
+        .def("train_interface", [](py::object self) {
+            Manager &mgr = self.cast<Manager &>();
+            madrona::py::TrainInterface ti = mgr.trainInterface();
+            auto named = [&](const std::vector<madrona::py::NamedTensor> &v) {
+                py::dict d;
+                for (const auto &nt : v) d[nt.name] = wrap(self, nt.tensor);
+                return d;
+            };
+            py::dict in, out, ck, r;
+            in["actions"] = named(ti.stepInputs().actions);
+            in["resets"] = wrap(self, ti.stepInputs().resets);
+            in["pbt"] = named(ti.stepInputs().pbt);
+            out["observations"] = named(ti.stepOutputs().observations);
+            out["rewards"] = wrap(self, ti.stepOutputs().rewards);
+            out["dones"] = wrap(self, ti.stepOutputs().dones);
+            out["pbt"] = named(ti.stepOutputs().pbt);
+            ck["checkpoint_data"] = wrap(self, ti.checkpointing().checkpointData);
+            r["step_inputs"] = in; r["step_outputs"] = out; r["checkpointing"] = ck;
+            return r;
+        })
+        // the bodies of the XLA GPU custom calls (src/mgr.hpp:44-50); `buffers` = device pointers
+#define HS_JAX(pyname, method)                                                                    \
+        .def(pyname, [](Manager &mgr, uintptr_t stream, std::vector<uintptr_t> buffers) {        \
+                 std::vector<void *> b(buffers.size());                                          \
+                 for (size_t i = 0; i < buffers.size(); i++) b[i] = (void *)buffers[i];          \
+                 mgr.method((cudaStream_t)stream, b.data());                                     \
+             }, py::arg("stream"), py::arg("buffers"))
+        HS_JAX("gpu_jax_init", gpuJAXInit)
+        HS_JAX("gpu_jax_step", gpuJAXStep)
+        HS_JAX("gpu_jax_save_checkpoints", gpuJAXSaveCheckpoints)
+        HS_JAX("gpu_jax_load_checkpoints", gpuJAXLoadCheckpoints)
+#undef HS_JAX
         // ---- extensions ----------------------------------------------------------------
         .def("step_async", [](Manager &mgr, uintptr_t stream) { mgr.stepAsync((void *)stream); },
              py::arg("stream") = 0)

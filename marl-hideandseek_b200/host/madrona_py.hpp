@@ -8,6 +8,7 @@
 #include <array>
 #include <cstdint>
 #include <initializer_list>
+#include <vector>
 
 namespace madrona {
 
@@ -58,6 +59,47 @@ private:
     int gpu_id_;
     int64_t num_dimensions_;
     std::array<int64_t, maxDimensions> dimensions_;
+};
+
+// The training-loop view of a simulator (M/include/madrona/py/utils.hpp:143-195): which tensors
+// are step inputs, which are outputs, and the checkpoint blob.  Value types here (std::vector
+// where the reference holds Span + pimpl); same member names.
+struct NamedTensor {
+    const char *name;
+    Tensor tensor;
+};
+
+struct TrainStepInputInterface {
+    std::vector<NamedTensor> actions;
+    Tensor resets;
+    Tensor simCtrl;
+    std::vector<NamedTensor> pbt;
+};
+
+struct TrainStepOutputInterface {
+    std::vector<NamedTensor> observations;
+    Tensor rewards;
+    Tensor dones;
+    std::vector<NamedTensor> stats;
+    std::vector<NamedTensor> pbt;
+};
+
+struct TrainCheckpointingInterface {
+    Tensor checkpointData;
+};
+
+class TrainInterface {
+public:
+    TrainInterface(TrainStepInputInterface in, TrainStepOutputInterface out, TrainCheckpointingInterface ckpt)
+        : in_(std::move(in)), out_(std::move(out)), ckpt_(ckpt) {}
+    const TrainStepInputInterface &stepInputs() const { return in_; }
+    const TrainStepOutputInterface &stepOutputs() const { return out_; }
+    const TrainCheckpointingInterface &checkpointing() const { return ckpt_; }
+
+private:
+    TrainStepInputInterface in_;
+    TrainStepOutputInterface out_;
+    TrainCheckpointingInterface ckpt_;
 };
 
 }  // namespace py

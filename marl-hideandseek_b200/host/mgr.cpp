@@ -165,6 +165,67 @@ void Manager::setAction(madrona::CountT agent_idx, int32_t x, int32_t y, int32_t
     req(hs_set_action(impl_->sim, agent_idx, x, y, r, g ? 1 : 0, l ? 1 : 0), "hs_set_action");
 }
 
+// src/mgr.cpp:987-1060 -> CUDAImpl::gpuStream* (src/mgr.cpp:365-437)
+void Manager::gpuJAXInit(cudaStream_t strm, void **buffers)
+{
+    req(hs_jax_init(impl_->sim, strm, buffers), "hs_jax_init");
+}
+
+void Manager::gpuJAXStep(cudaStream_t strm, void **buffers)
+{
+    req(hs_jax_step(impl_->sim, strm, buffers), "hs_jax_step");
+}
+
+void Manager::gpuJAXSaveCheckpoints(cudaStream_t strm, void **buffers)
+{
+    req(hs_jax_save_checkpoints(impl_->sim, strm, buffers), "hs_jax_save_checkpoints");
+}
+
+void Manager::gpuJAXLoadCheckpoints(cudaStream_t strm, void **buffers)
+{
+    req(hs_jax_load_checkpoints(impl_->sim, strm, buffers), "hs_jax_load_checkpoints");
+}
+
+// src/mgr.cpp:1333-1336: no simulator control tensor
+Tensor Manager::simControlTensor() const
+{
+    const int64_t dims[1] = {0};
+    return Tensor(nullptr, TensorElementType::Int32, dims, 1, -1);
+}
+
+// src/mgr.cpp:1338-1375: same names, same order
+madrona::py::TrainInterface Manager::trainInterface() const
+{
+    using namespace madrona::py;
+    return TrainInterface(
+        TrainStepInputInterface{
+            {{"actions", actionTensor()}},
+            resetTensor(),
+            simControlTensor(),
+            {{"policy_assignments", policyAssignmentsTensor()}},
+        },
+        TrainStepOutputInterface{
+            {
+                {"prep_counter", prepCounterTensor()},
+                {"self_data", selfDataTensor()},
+                {"self_type", selfTypeTensor()},
+                {"self_mask", selfMaskTensor()},
+                {"self_lidar", lidarTensor()},
+                {"agent_data", agentDataTensor()},
+                {"box_data", boxDataTensor()},
+                {"ramp_data", rampDataTensor()},
+                {"vis_agents_mask", visibleAgentsMaskTensor()},
+                {"vis_boxes_mask", visibleBoxesMaskTensor()},
+                {"vis_ramps_mask", visibleRampsMaskTensor()},
+            },
+            rewardTensor(),
+            doneTensor(),
+            {},
+            {{"episode_results", episodeResultTensor()}},
+        },
+        TrainCheckpointingInterface{checkpointTensor()});
+}
+
 void *Manager::handle() const { return impl_->sim; }
 uint32_t Manager::numWorlds() const { return impl_->cfg.numWorlds; }
 uint32_t Manager::agentsPerWorld() const { return impl_->cfg.maxHiders + impl_->cfg.maxSeekers; }

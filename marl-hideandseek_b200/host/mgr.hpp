@@ -19,6 +19,9 @@
 
 namespace madrona::render { struct APIBackend; struct GPUDevice; class RenderManager; }
 
+// the CUDA runtime's own typedef, restated so this header needs no CUDA include
+typedef struct CUstream_st *cudaStream_t;
+
 namespace GPUHideSeek {
 
 class Manager {
@@ -54,6 +57,14 @@ public:
     void loadCheckpoint(madrona::CountT world_idx);
     void loadCheckpoints();
 
+    // XLA custom-call bodies (src/mgr.hpp:44-50, src/mgr.cpp:365-437): `buffers` = device
+    // pointers in the order documented at hs_jax_* in include/hideseek/c_api.h; everything is
+    // enqueued on `strm`, only gpuJAXInit waits for it.
+    void gpuJAXInit(cudaStream_t strm, void **buffers);
+    void gpuJAXStep(cudaStream_t strm, void **buffers);
+    void gpuJAXSaveCheckpoints(cudaStream_t strm, void **buffers);
+    void gpuJAXLoadCheckpoints(cudaStream_t strm, void **buffers);
+
     madrona::py::Tensor resetTensor() const;
     madrona::py::Tensor doneTensor() const;
     madrona::py::Tensor prepCounterTensor() const;
@@ -85,6 +96,9 @@ public:
 
     madrona::py::Tensor policyAssignmentsTensor() const;
     madrona::py::Tensor episodeResultTensor() const;
+    madrona::py::Tensor simControlTensor() const;       // empty, as in the reference
+
+    madrona::py::TrainInterface trainInterface() const;
 
     // ---- extensions (not in the reference) -------------------------------------------------
     // Asynchronous step on a caller stream (cudaStream_t as void*) + explicit wait; the
