@@ -39,6 +39,7 @@ struct RaySmem {
     float agentRot[kMaxAgents][4];
     int agentSlot[kMaxAgents];
     int agentType[kMaxAgents];
+    int agentSkipLeaf[kMaxAgents];        // the agent's own leaf when its rays provably miss it, else -1
     // visibility ray queue
     float visDir[kMaxVisRays][3];
     uint16_t visInfo[kMaxVisRays];        // agent k | target slot << 3 | seesHiderCandidate << 11
@@ -99,6 +100,29 @@ __device__ __forceinline__ bool traceLeafS(const uint32_t *blob, const AssetTabl
     }
     if (!entered) return false;
     *hit_t = tfirst;
+    return true;
+}
+
+// True when `o` lies strictly inside the convex hull of `leaf` (every face plane at least 1e-4
+// away in object space).  traceLeafS then returns false for EVERY direction from `o`: no entering
+// plane has t >= 0, so the "only back faces" rule rejects the leaf.  Every ray an agent casts
+// starts at its own centre, so its own leaf — always the nearest slab entry (t = 0) — can be left
+// out of the query without changing any result.
+__device__ inline bool originInsideLeaf(const uint32_t *blob, const AssetTable &AT, int leaf, Vec3 o)
+{
+    const float *L = leafF(blob, leaf);
+    int obj = int(blob[kBvhLeafOff + leaf * kLeafWords + kLeafInfo] >> 8) & 0xFF;
+    if (AT.obj[obj].primType != 2) return false;
+    Vec3 pos = {L[kLeafPos], L[kLeafPos + 1], L[kLeafPos + 2]};
+    Quat rot = {L[kLeafRot], L[kLeafRot + 1], L[kLeafRot + 2], L[kLeafRot + 3]};
+    Vec3 scale = {L[kLeafScale], L[kLeafScale + 1], L[kLeafScale + 2]};
+    Vec3 oo = rotate(qinv(rot), o - pos);
+    oo.x /= scale.x; oo.y /= scale.y; oo.z /= scale.z;
+    const HullData &H = AT.hull[obj];
+    for (int f = 0; f < H.numFaces; f++) {
+        Vec3 n = {H.planes[f][0], H.planes[f][1], H.planes[f][2]};
+        if (!(H.planes[f][3] - dot(n, oo) > 1e-4f)) return false;
+    }
     return true;
 }
 
@@ -192,7 +216,7 @@ __device__ inline int traceRayWarp(const uint32_t *blob, const AssetTable &AT, b
 // leaves, which changes neither a lidar depth nor — short of two bodies sharing their entry face
 // at the hit point — a visibility bit (tests/test_ray_order_gpu.py compares both modes bit-wise).
 __device__ inline int traceRayFlat(const uint32_t *blob, const AssetTable &AT, bool active,
-                                   Vec3 o, Vec3 d, float t_max, float *out_t)
+                                   Vec3 o, Vec3 d, float t_max, float *out_t, int skipLeaf = -1)
 {
     const Vec3 inv = {1.f / d.x, 1.f / d.y, 1.f / d.z};
     const int numLeaves = min((int)blob[1], kMaxBodies);
@@ -213,7 +237,7 @@ __device__ inline int traceRayFlat(const uint32_t *blob, const AssetTable &AT, b
         float a;
         bool ok;
         HS_LEAF_SLAB(L, a, ok)
-        if (ok && active) {
+        if (ok && active && l != skipLeaf) {
             mask |= 1ull << l;
             if (a < bestA) { bestA = a; bestL = l; }
         }
@@ -260,9 +284,9 @@ __device__ inline int traceRayFlat(const uint32_t *blob, const AssetTable &AT, b
 // identically); true is the flat nearest-first query and the default (hs_sim.cu: HIDESEEK_RAY_ORDER=reference selects the other at run time).
 template <bool kNearestFirst>
 __device__ __forceinline__ int traceRaySel(const uint32_t *blob, const AssetTable &AT, bool active,
-                                           Vec3 o, Vec3 d, float t_max, float *out_t)
+                                           Vec3 o, Vec3 d, float t_max, float *out_t, int skipLeaf = -1)
 {
-    if (kNearestFirst) return traceRayFlat(blob, AT, active, o, d, t_max, out_t);
+    if (kNearestFirst) return traceRayFlat(blob, AT, active, o, d, t_max, out_t, skipLeaf);
     return traceRayWarp(blob, AT, active, o, d, t_max, out_t);
 }
 
@@ -303,6 +327,15 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
     }
     if (tid == 0) sm.numVis = 0;
     __syncthreads();
+    if (tid < A) {
+        int skip = -1;
+        if (sm.agentSlot[tid] >= 0) {
+            const int leaf = metaLeaf(META(S, sm.agentSlot[tid], w));
+            Vec3 p = {sm.agentPos[tid][0], sm.agentPos[tid][1], sm.agentPos[tid][2]};
+            if (leaf < numLeaves && originInsideLeaf(sm.bvh, sm.assets, leaf, p)) skip = leaf;
+        }
+        sm.agentSkipLeaf[tid] = skip;
+    }
 
     // ---- visibility: cone test per (agent, target); survivors join the ray queue --------------
     constexpr int kTargets = kMaxBoxes + kMaxRamps + kMaxAgents;      // 17 lanes of the old kernel
@@ -379,7 +412,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
             o = {sm.agentPos[k][0], sm.agentPos[k][1], sm.agentPos[k][2]};
         }
         float t = 0.f;
-        int hit = traceRaySel<kNearestFirst>(sm.bvh, sm.assets, active, o, d, tmax, &t);
+        int hit = traceRaySel<kNearestFirst>(sm.bvh, sm.assets, active, o, d, tmax, &t, active ? sm.agentSkipLeaf[k] : -1);
         if (!active) continue;
         if (isLidar) {
             S.exLidar[(size_t(w) * A + k) * 30 + (r - k * 30)] = hit < 0 ? 0.f : t;
@@ -425,11 +458,12 @@ __global__ void __launch_bounds__(kRewardWarps * 32) k_rewards(DeviceState S, fl
     const int numHiders = WI(S, WF_NUM_HIDERS, wc), numSeekers = WI(S, WF_NUM_SEEKERS, wc);
 
     bool active = valid && lg < numHiders * numSeekers;
-    int hslot = -1;
+    int hslot = -1, skip = -1;
     Vec3 spos = {0.f, 0.f, 0.f}, toHider = {1.f, 0.f, 0.f};
     if (active) {
         int si = lg / numHiders, hi = lg - si * numHiders;
         int sslot = WB(S, WB_SEEKER_SLOT + si, w);
+        skip = metaLeaf(META(S, sslot, w));
         hslot = WB(S, WB_HIDER_SLOT + hi, w);
         const Pose sp = loadPose(S, REC_POSE, sslot, w);
         spos = sp.x;
@@ -437,9 +471,10 @@ __global__ void __launch_bounds__(kRewardWarps * 32) k_rewards(DeviceState S, fl
         toHider = loadPos(S, hslot, w) - spos;
         float cosA = dot(normalize(toHider), sfwd);
         if (cosA < cosThreshold) active = false;
+        else if (!originInsideLeaf(BVH(S, w), s_assets, skip, spos)) skip = -1;
     }
     float t;
-    int hit = traceRaySel<kNearestFirst>(BVH(S, wc), s_assets, active, spos, toHider, 1.f, &t);
+    int hit = traceRaySel<kNearestFirst>(BVH(S, wc), s_assets, active, spos, toHider, 1.f, &t, skip);
     const unsigned seen = __ballot_sync(0xFFFFFFFFu, active && hit == hslot);
     if (!valid) return;
     if (seen & gmask) teamReward = -1.f;
