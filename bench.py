@@ -123,6 +123,9 @@ def kernel_alg_bytes(name, A, E, C, K):
         "k_broadphase": E * (24 + 4) + C * 2,
         "k_substep": E * (posevel + 24 + 4 + pose + 2 * pose + 24),
         "k_narrowphase": C * (2 + 2 * (40 + 4)) + K * 84,
+        # fused solvePositions + setVelocities + solveVelocities: the contact row is read once
+        "k_solve": K * (84 + 2 * (3 * pose + 4) + 2 * pose) + E * (2 * pose + 24)
+                   + K * (2 * (2 * pose + 24 + 24 + 4) + 2 * 24),
         "k_solve_positions": K * (84 + 2 * (3 * pose + 4) + 2 * pose),
         "k_set_velocities": E * (2 * pose + 24),
         "k_solve_velocities": K * (84 + 2 * (2 * pose + 24 + 24 + 4) + 2 * 24),

@@ -311,10 +311,19 @@ extern "C" int hs_last_step_launches(hs_sim *sim) { return sim->lastLaunches; }
 // ---- launch sequence ------------------------------------------------------------
 namespace {
 
+// HIDESEEK_FUSED_SOLVE=0 launches solvePositions / setVelocities / solveVelocities as three kernels
+// (the pre-fusion pipeline, kept for A/B measurements); default is the fused k_solve.
+static bool fusedSolveDefault()
+{
+    const char *e = getenv("HIDESEEK_FUSED_SOLVE");
+    return !(e && e[0] == '0');
+}
+
 struct Launcher {
     DeviceState S;
     cudaStream_t st;
     int count = 0;
+    bool fusedSolve = fusedSolveDefault();
     std::vector<cudaEvent_t> *events = nullptr;     // profiling mode: one event after each launch
     std::vector<const char *> *names = nullptr;
     void mark(const char *name)
@@ -369,9 +378,13 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
     for (int i = 0; i < kSubsteps; i++) {
         k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep");
         k_narrowphase<<<(L.N() + kNpWorlds - 1) / kNpWorlds, kNpThreads, sizeof(NpSmem), L.st>>>(L.S); L.mark("k_narrowphase");
-        k_solve_positions<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_positions");
-        k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_set_velocities");
-        k_solve_velocities<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_velocities");
+        if (L.fusedSolve) {
+            k_solve<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve");
+        } else {
+            k_solve_positions<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_positions");
+            k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_set_velocities");
+            k_solve_velocities<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_velocities");
+        }
     }
     launchBroadphaseSetup(L, false);
     if (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) {

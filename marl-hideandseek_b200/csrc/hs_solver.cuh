@@ -364,6 +364,27 @@ __device__ __forceinline__ int buildLevels(const DeviceState &S, int w, SolveGro
     return K;
 }
 
+// joints in creation order (at most one Fixed joint per agent; rare), after every contact
+__device__ inline void solveJoints(const DeviceState &S, int w, int lg)
+{
+    if (lg != 0) return;
+    const int na = WI(S, WF_NUM_AGENTS, w);
+    const int nDyn = WI(S, WF_NUM_DYN, w);
+    int lastSeq = -1;
+    for (int it = 0; it < na; it++) {
+        int best = -1, bestSeq = 0x7FFFFFFF;
+        for (int k = 0; k < na; k++) {
+            uint32_t jm = JMETA(S, k, w);
+            if (jm == 0xFFFFFFFFu) continue;
+            int seq = int(jm >> 16);
+            if (seq > lastSeq && seq < bestSeq) { bestSeq = seq; best = k; }
+        }
+        if (best < 0) break;
+        lastSeq = bestSeq;
+        handleFixedJoint(S, w, best, nDyn + best, int(JMETA(S, best, w) & 0xFF));
+    }
+}
+
 // solvePositions
 __global__ void __launch_bounds__(kSolveThreads) k_solve_positions(DeviceState S)
 {
@@ -393,24 +414,21 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve_positions(DeviceState S
         for (int k = 0; k < K; k++) handleContact(S, w, g.cm[k], contacts + size_t(g.cm[k] >> 24) * kContactWords, true, true);
     __syncwarp(gmask);
 
-    // joints in creation order (at most one Fixed joint per agent; rare)
-    if (lg == 0) {
-        const int na = WI(S, WF_NUM_AGENTS, w);
-        const int nDyn = WI(S, WF_NUM_DYN, w);
-        int lastSeq = -1;
-        for (int it = 0; it < na; it++) {
-            int best = -1, bestSeq = 0x7FFFFFFF;
-            for (int k = 0; k < na; k++) {
-                uint32_t jm = JMETA(S, k, w);
-                if (jm == 0xFFFFFFFFu) continue;
-                int seq = int(jm >> 16);
-                if (seq > lastSeq && seq < bestSeq) { bestSeq = seq; best = k; }
-            }
-            if (best < 0) break;
-            lastSeq = bestSeq;
-            handleFixedJoint(S, w, best, nDyn + best, int(JMETA(S, best, w) & 0xFF));
-        }
-    }
+    solveJoints(S, w, lg);
+}
+
+// setVelocities (xpbd.cpp:738-779) for one body
+__device__ __forceinline__ void setBodyVelocity(const DeviceState &S, int s, int w)
+{
+    const float h = substepH();
+    const Pose cur = loadPose(S, REC_POSE, s, w), prev = loadPose(S, REC_PREV, s, w);
+    Vec3 x = cur.x, xp = prev.x;
+    Quat q = cur.q, qp = prev.q;
+    Quat dq;
+    if (q.w != qp.w || q.x != qp.x || q.y != qp.y || q.z != qp.z) dq = q * qinv(qp);
+    else dq = {1.f, 0.f, 0.f, 0.f};
+    Vec3 newOmega = (2.f / h) * v3(dq.x, dq.y, dq.z);
+    storeVel6(S, REC_VEL, s, w, (x - xp) / h, dq.w > 0.f ? newOmega : -newOmega);
 }
 
 // setVelocities: one thread per (slot, world)
@@ -421,16 +439,7 @@ __global__ void k_set_velocities(DeviceState S)
     if (idx >= (long long)kMaxBodies * N) return;
     int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
     if (s >= WI(S, WF_NUM_BODIES, w)) return;
-
-    const float h = substepH();
-    const Pose cur = loadPose(S, REC_POSE, s, w), prev = loadPose(S, REC_PREV, s, w);
-    Vec3 x = cur.x, xp = prev.x;
-    Quat q = cur.q, qp = prev.q;
-    Quat dq;
-    if (q.w != qp.w || q.x != qp.x || q.y != qp.y || q.z != qp.z) dq = q * qinv(qp);
-    else dq = {1.f, 0.f, 0.f, 0.f};
-    Vec3 newOmega = (2.f / h) * v3(dq.x, dq.y, dq.z);
-    storeVel6(S, REC_VEL, s, w, (x - xp) / h, dq.w > 0.f ? newOmega : -newOmega);
+    setBodyVelocity(S, s, w);
 }
 
 __device__ __forceinline__ Vec3 relVel(Vec3 v1, Vec3 v2, Vec3 o1, Vec3 o2, Vec3 d1, Vec3 d2)
@@ -546,6 +555,74 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve_velocities(DeviceState 
             uint32_t cm = g.cm[k];
             solveContactVelocity(S, w, cm, contacts + size_t(cm >> 24) * kContactWords,
                                  g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
+        }
+        __syncwarp(gmask);
+    }
+    if (maxLvl < 0 && lg == 0)
+        for (int k = 0; k < K; k++) solveContactVelocity(S, w, g.cm[k], contacts + size_t(g.cm[k] >> 24) * kContactWords, true, true);
+    if (lg == 0) WI(S, WF_NUM_CONTACTS, w) = K;
+}
+
+// solvePositions + setVelocities + solveVelocities of one substep in ONE launch: the three stages
+// of a world are consecutive and touch only that world, so the same 8-lane group runs them back
+// to back.  The level schedule is built once, with the position-pass rule; it is also a valid
+// schedule for the velocity pass, whose conflicts (contacts sharing a non-Static body) are a
+// subset of the position pass's, so both passes reproduce the serial creation-order sweep.
+__global__ void __launch_bounds__(kSolveThreads) k_solve(DeviceState S)
+{
+    __shared__ SolveGroupSmem sg[kSolveGroups];
+    __shared__ unsigned long long s_static[kSolveGroups];
+    const int lane = threadIdx.x & 31;
+    const int lg = lane % kSolveLanes;
+    const int gshift = lane - lg;
+    const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
+    const int grp = threadIdx.x / kSolveLanes;
+    const int w = blockIdx.x * kSolveGroups + grp;
+    if (w >= S.p.numWorlds) return;
+    SolveGroupSmem &g = sg[grp];
+    const int nb = WI(S, WF_NUM_BODIES, w);
+
+    // Static bodies (never written by the velocity pass)
+    {
+        unsigned long long mine = 0ull;
+        for (int s = lg; s < nb; s += kSolveLanes)
+            if (metaResp(META(S, s, w)) == RESP_STATIC) mine |= 1ull << s;
+#pragma unroll
+        for (int o = kSolveLanes / 2; o > 0; o >>= 1) mine |= __shfl_xor_sync(gmask, mine, o);
+        if (lg == 0) s_static[grp] = mine;
+    }
+
+    int maxLvl;
+    const int K = buildLevels<false>(S, w, g, lg, gmask, gshift, &maxLvl);
+    float *contacts = S.contact + size_t(w) * kMaxCand * kContactWords;
+    // ---- positions ----------------------------------------------------------------------------
+    for (int lv = 0; lv <= maxLvl; lv++) {
+        const int end = K ? g.lvlStart[lv + 1] : 0;
+        for (int i = g.lvlStart[lv] + lg; i < end; i += kSolveLanes) {
+            const int k = g.order[i];
+            uint32_t cm = g.cm[k];
+            handleContact(S, w, cm, contacts + size_t(cm >> 24) * kContactWords,
+                          g.blvl[cm & 0xFF] != 0xFF, g.blvl[(cm >> 8) & 0xFF] != 0xFF);
+        }
+        __syncwarp(gmask);
+    }
+    if (maxLvl < 0 && lg == 0)
+        for (int k = 0; k < K; k++) handleContact(S, w, g.cm[k], contacts + size_t(g.cm[k] >> 24) * kContactWords, true, true);
+    __syncwarp(gmask);
+    solveJoints(S, w, lg);
+    __syncwarp(gmask);
+    // ---- velocities from the position change ----------------------------------------------------
+    for (int s = lg; s < nb; s += kSolveLanes) setBodyVelocity(S, s, w);
+    __syncwarp(gmask);
+    // ---- velocity pass ----------------------------------------------------------------------------
+    const unsigned long long st = s_static[grp];
+    for (int lv = 0; lv <= maxLvl; lv++) {
+        const int end = K ? g.lvlStart[lv + 1] : 0;
+        for (int i = g.lvlStart[lv] + lg; i < end; i += kSolveLanes) {
+            const int k = g.order[i];
+            uint32_t cm = g.cm[k];
+            solveContactVelocity(S, w, cm, contacts + size_t(cm >> 24) * kContactWords,
+                                 !((st >> (cm & 0xFF)) & 1ull), !((st >> ((cm >> 8) & 0xFF)) & 1ull));
         }
         __syncwarp(gmask);
     }
