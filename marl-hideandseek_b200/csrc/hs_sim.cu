@@ -52,6 +52,10 @@ struct hs_sim {
     int slices = 1, branches = 1;
     cudaStream_t sliceStream[8] = {};
     cudaEvent_t forkEvent = nullptr, joinEvent[8] = {};
+    // per branch: two side streams so observations / debug positions run beside the ray kernel
+    cudaStream_t auxStream[8][2] = {};
+    cudaEvent_t auxFork[8] = {}, auxJoin[8][2] = {};
+    bool obsFork = true;
     bool inited = false;
     float cosThreshold = 0.f;
 };
@@ -172,6 +176,14 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
             HS_CUDA(cudaStreamCreateWithFlags(&sim->sliceStream[b], cudaStreamNonBlocking));
             HS_CUDA(cudaEventCreateWithFlags(&sim->joinEvent[b], cudaEventDisableTiming));
         }
+        if (const char *e = getenv("HIDESEEK_OBS_FORK")) sim->obsFork = e[0] != '0';
+        for (int b = 0; b < br && sim->obsFork; b++) {
+            HS_CUDA(cudaEventCreateWithFlags(&sim->auxFork[b], cudaEventDisableTiming));
+            for (int i = 0; i < 2; i++) {
+                HS_CUDA(cudaStreamCreateWithFlags(&sim->auxStream[b][i], cudaStreamNonBlocking));
+                HS_CUDA(cudaEventCreateWithFlags(&sim->auxJoin[b][i], cudaEventDisableTiming));
+            }
+        }
     }
     {
         // cosf(toRadians(135.f / 2.f)) as the reference's compiler folds it (src/sim.cpp:582,767)
@@ -191,6 +203,13 @@ extern "C" void hs_destroy(hs_sim *sim)
     if (sim->stepGraph) cudaGraphExecDestroy(sim->stepGraph);
     if (sim->graphStream) cudaStreamDestroy(sim->graphStream);
     if (sim->forkEvent) cudaEventDestroy(sim->forkEvent);
+    for (int b = 0; b < 8; b++) {
+        if (sim->auxFork[b]) cudaEventDestroy(sim->auxFork[b]);
+        for (int i = 0; i < 2; i++) {
+            if (sim->auxStream[b][i]) cudaStreamDestroy(sim->auxStream[b][i]);
+            if (sim->auxJoin[b][i]) cudaEventDestroy(sim->auxJoin[b][i]);
+        }
+    }
     for (int b = 1; b < 8; b++) {
         if (sim->sliceStream[b]) cudaStreamDestroy(sim->sliceStream[b]);
         if (sim->joinEvent[b]) cudaEventDestroy(sim->joinEvent[b]);
@@ -324,6 +343,9 @@ struct Launcher {
     cudaStream_t st;
     int count = 0;
     bool fusedSolve = fusedSolveDefault();
+    // graph capture only: side streams + events for the independent observation-stage kernels
+    cudaStream_t aux[2] = {nullptr, nullptr};
+    cudaEvent_t auxFork = nullptr, auxJoin[2] = {nullptr, nullptr};
     std::vector<cudaEvent_t> *events = nullptr;     // profiling mode: one event after each launch
     std::vector<const char *> *names = nullptr;
     void mark(const char *name)
@@ -359,13 +381,28 @@ void launchBroadphaseSetup(Launcher &L, bool mayRebuild, bool onlyIfReset = fals
 }
 
 // observationsTasks (src/sim.cpp:1232-1293)
+// collectObservations, visibility + lidar and the debug positions only read the world state and
+// write disjoint exports, so inside the step graph they run as three parallel nodes.
 void launchObservations(Launcher &L, float cosThr, bool nearestFirst)
 {
-    k_observations<<<unsigned(((long long)L.N() * L.S.p.agentsPerWorld * 18 + 255) / 256), 256, 0, L.st>>>(L.S); L.mark("k_observations");
+    const bool fork = L.aux[0] != nullptr;
+    cudaStream_t so = fork ? L.aux[0] : L.st, sd = fork ? L.aux[1] : L.st;
+    if (fork) {
+        cudaEventRecord(L.auxFork, L.st);
+        cudaStreamWaitEvent(L.aux[0], L.auxFork, 0);
+        cudaStreamWaitEvent(L.aux[1], L.auxFork, 0);
+    }
+    k_observations<<<unsigned(((long long)L.N() * L.S.p.agentsPerWorld * 18 + 255) / 256), 256, 0, so>>>(L.S); L.mark("k_observations");
     if (nearestFirst) k_rays<true><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
     else k_rays<false><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
     L.mark("k_rays");
-    k_debug_positions<<<L.gWorld(), 128, 0, L.st>>>(L.S); L.mark("k_debug_positions");
+    k_debug_positions<<<L.gWorld(), 128, 0, sd>>>(L.S); L.mark("k_debug_positions");
+    if (fork) {
+        for (int i = 0; i < 2; i++) {
+            cudaEventRecord(L.auxJoin[i], L.aux[i]);
+            cudaStreamWaitEvent(L.st, L.auxJoin[i], 0);
+        }
+    }
 }
 
 // Step task graph (src/sim.cpp:1307-1313), node order of SURVEY.md §3.3
@@ -501,6 +538,10 @@ extern "C" int hs_step(hs_sim *sim, void *stream)
             const int b = sl % BR;
             cudaStream_t sb = b == 0 ? sim->graphStream : sim->sliceStream[b];
             Launcher L{sliceOf(sim->S, begin, count), sb};
+            if (sim->obsFork) {
+                L.aux[0] = sim->auxStream[b][0]; L.aux[1] = sim->auxStream[b][1];
+                L.auxFork = sim->auxFork[b]; L.auxJoin[0] = sim->auxJoin[b][0]; L.auxJoin[1] = sim->auxJoin[b][1];
+            }
             launchStep(L, sim->cosThreshold, sim->raysNearestFirst);
             launches += L.count;
         }
