@@ -350,7 +350,8 @@ def run_ours(args):
                 "d2h_bytes_per_step": R * 8, "steps": e2e_steps,
                 "how": "hs_step_host: pinned host actions -> H2D, step graph, reward+done D2H, "
                        "stream sync every step", "reward_checksum": checksum},
-        "gpu_launches": sim.last_step_launches() * args.steps,
+        "gpu_launches": sim.last_step_launches() * args.steps * world,     # whole job
+        "gpu_launches_per_rank": sim.last_step_launches() * args.steps,
         "launches_per_step": sim.last_step_launches(),
         "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "overflow": sim.overflow_count(),
