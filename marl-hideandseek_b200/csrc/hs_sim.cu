@@ -392,7 +392,11 @@ void launchObservations(Launcher &L, float cosThr, bool nearestFirst)
         cudaStreamWaitEvent(L.aux[0], L.auxFork, 0);
         cudaStreamWaitEvent(L.aux[1], L.auxFork, 0);
     }
-    k_observations<<<unsigned(((long long)L.N() * L.S.p.agentsPerWorld * 18 + 255) / 256), 256, 0, so>>>(L.S); L.mark("k_observations");
+    {
+        const long long R = (long long)L.N() * L.S.p.agentsPerWorld;
+        const long long nb = obsBlocks(R) + obsBlocks(R * kMaxBoxes) + obsBlocks(R * kMaxRamps) + obsBlocks(R * kMaxAgents);
+        k_observations<<<unsigned(nb), kObsThreads, 0, so>>>(L.S);
+    } L.mark("k_observations");
     if (nearestFirst) k_rays<true><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
     else k_rays<false><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
     L.mark("k_rays");
