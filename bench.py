@@ -346,8 +346,9 @@ def run_ours(args):
                    "worlds_per_gpu": N, "agents_per_world": A, "sharding": f"worlds x{world}",
                    "l2": "per-GPU state (BVH 208 MB + body records 186 MB + contacts 328 MB + exports 81 MB) exceeds the 126 MB L2",
                    "mean_bodies": E, "mean_candidates": C, "mean_contacts": K},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": R * 5 * 4,
-                "d2h_bytes_per_step": R * 8, "steps": e2e_steps,
+        # bytes are whole-job totals like `value` (every rank copies its own shard's tensors)
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": R * 5 * 4 * world,
+                "d2h_bytes_per_step": R * 8 * world, "steps": e2e_steps,
                 "how": "hs_step_host: pinned host actions -> H2D, step graph, reward+done D2H, "
                        "stream sync every step", "reward_checksum": checksum},
         "gpu_launches": sim.last_step_launches() * args.steps * world,     # whole job
