@@ -119,3 +119,15 @@ def test_debug_levels_2_to_8():
     # episode rollover (level 5 leaks its plane across a reset in the reference).
     _run_pair(8, seed=2, flags=0, steps=150, hs=(2, 2), sk=(2, 2), use_grab_lock=True, check_every=5,
               levels=[2, 3, 4, 5, 6, 7, 8, 1], min_agents=0)
+
+
+def test_ragged_worlds_with_empty_teams():
+    # edge cases the reference allows: teams of 0..3 (a world may have no hider, no seeker or no
+    # agent at all), a world count that is no multiple of any tile size, frequent resets so the
+    # agent count of a row changes during the run
+    _run_pair(37, seed=11, flags=0, steps=60, hs=(0, 3), sk=(0, 3), use_grab_lock=True, check_every=6,
+              reset_prob=0.1, min_agents=0)
+
+
+def test_single_world():
+    _run_pair(1, seed=4, flags=0, steps=40, check_every=8)
