@@ -132,6 +132,7 @@ def kernel_alg_bytes(name, A, E, C, K):
         "k_zero_agent_vel": A * 48,
         "k_rewards": A * (pose + 8),
         "k_reset": 4,
+        "k_reset_worlds": 0,
         "k_observations": A * (13 + 70 + 153 + 28) * 4 + E * posevel,
         # leaf records in (40 B + meta), 30 lidar floats + 16 visibility flags x4 B out
         "k_rays": A * (120 + 64) + E * (40 + 4),

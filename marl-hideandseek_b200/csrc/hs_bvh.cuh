@@ -136,11 +136,9 @@ __global__ void k_leaf_refit(DeviceState S, bool onlyIfReset)
     }
 }
 
-// BVH::rebuild — one thread per world that has force_rebuild set.
-__global__ void k_bvh_rebuild(DeviceState S)
+// BVH::rebuild of one world (no-op unless force_rebuild is set).
+__device__ inline void rebuildWorldBvh(const DeviceState &S, int w)
 {
-    int w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= S.p.numWorlds) return;
     uint32_t *blob = BVH(S, w);
     if (blob[2] == 0) return;
     blob[2] = 0;
@@ -273,6 +271,14 @@ __global__ void k_bvh_rebuild(DeviceState S)
             }
         }
     }
+}
+
+// One thread per world; worlds without a pending rebuild return at once.
+__global__ void k_bvh_rebuild(DeviceState S)
+{
+    int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= S.p.numWorlds) return;
+    rebuildWorldBvh(S, w);
 }
 
 }  // namespace hs

@@ -343,11 +343,17 @@ __device__ inline void generateTrainingWorld(const DeviceState &S, int w, Rng &e
         slot++; leaf++;
     }
 
+    // any-overlap is order-free, so the scan has no early exit and no per-component branches: the
+    // loads of several boxes are in flight together (this loop is the critical path of a reset)
     auto overlapsPlaced = [&](const AABB &a) {
+        bool any = false;
+#pragma unroll 4
         for (int i = 0; i < numPlaced; i++) {
-            if (aabbOverlaps(a, placed[i])) return true;
+            const AABB b = placed[i];
+            any |= (a.lo.x < b.hi.x) & (b.lo.x < a.hi.x) & (a.lo.y < b.hi.y) & (b.lo.y < a.hi.y) &
+                   (a.lo.z < b.hi.z) & (b.lo.z < a.hi.z);
         }
-        return false;
+        return any;
     };
 
     // shared rejection-sampling loop (level_gen.cpp:123-229, 266-292)
@@ -600,7 +606,13 @@ __device__ inline void regenerateWorld(const DeviceState &S, int w, const CkptRe
     ids.commit();
 }
 
-// resetSystem (src/sim.cpp:172-200), one thread per world.
+// resetSystem (src/sim.cpp:172-200) in two launches.  k_reset: one thread per world decides
+// (explicit trigger or episode end), advances the step counter of the worlds that carry on and
+// appends the others to a compact list.  k_reset_worlds: one thread per LISTED world runs the
+// serial level-generation program, so when only some worlds reset (training with staggered
+// episodes, the reset-heavy configuration) the warps doing the long program are full instead
+// of carrying 32 lanes for a few resetting worlds.  Worlds are independent, so the list order
+// (atomic, arbitrary) does not matter.
 __global__ void k_reset(DeviceState S)
 {
     int w = blockIdx.x * blockDim.x + threadIdx.x;
@@ -612,12 +624,36 @@ __global__ void k_reset(DeviceState S)
 
     if (level != 0) {
         S.exReset[w] = 0;
-        regenerateWorld(S, w, nullptr, level);
+        S.resetList[atomicAdd(S.resetCount, 1)] = uint32_t(w) | (uint32_t(level) << 24);
     } else {
         WI(S, WF_EPISODE_STEP, w) = step + 1;
         WI(S, WF_DID_RESET, w) = 0;
     }
     WI(S, WF_HIDER_REWARD, w) = __float_as_int(1.f);
+}
+
+// Launched with kResetSpread threads per world of the slice.  Level generation is a long,
+// branchy, per-world serial program: 32 worlds in one warp follow 32 different paths and the
+// warp executes their union (measured: 4.6 of 32 lanes active, ~7x the single-world
+// instruction count).  When few worlds reset, each gets a warp of its own (lane 0 works), which
+// removes that serialisation; when most worlds reset the dense mapping issues fewer
+// instructions in total and the GPU is full anyway.
+constexpr int kResetSpread = 32;
+
+__global__ void k_reset_worlds(DeviceState S)
+{
+    const int count = *S.resetCount;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int i;
+    if (count * 4 <= S.p.numWorlds) {
+        if (t % kResetSpread) return;
+        i = t / kResetSpread;
+    } else {
+        i = t;
+    }
+    if (i >= count) return;
+    const uint32_t e = S.resetList[i];
+    regenerateWorld(S, int(e & 0xFFFFFFu), nullptr, int(e >> 24));
 }
 
 }  // namespace hs

@@ -81,7 +81,7 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
 {
     if (!cfg || !out) { g_err = "hs_create: null argument"; return 1; }
     int A = cfg->max_hiders + cfg->max_seekers;
-    if (cfg->num_worlds <= 0 || A <= 0 || A > kMaxAgents || cfg->max_hiders > 3 || cfg->max_seekers > 3 ||
+    if (cfg->num_worlds <= 0 || cfg->num_worlds >= (1 << 24) || A <= 0 || A > kMaxAgents || cfg->max_hiders > 3 || cfg->max_seekers > 3 ||
         cfg->min_hiders > cfg->max_hiders || cfg->min_seekers > cfg->max_seekers) {
         g_err = "hs_create: invalid configuration";
         return 1;
@@ -109,6 +109,8 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     HS_TRY(devAlloc(sim, &S.jmeta, size_t(kMaxAgents) * N));
     HS_TRY(devAlloc(sim, &S.bvh, size_t(kBvhWords) * N));
     HS_TRY(devAlloc(sim, &S.dfsLeaf, size_t(kDfsStride) * N));
+    HS_TRY(devAlloc(sim, &S.resetList, N));
+    HS_TRY(devAlloc(sim, &S.resetCount, N));
     HS_TRY(devAlloc(sim, &S.cand, size_t(kMaxCand) * N));
     HS_TRY(devAlloc(sim, &S.contact, size_t(kMaxCand) * kContactWords * N));
     HS_TRY(devAlloc(sim, &S.cmeta, size_t(kMaxCand) * N));
@@ -409,6 +411,13 @@ void launchObservations(Launcher &L, float cosThr, bool nearestFirst)
     }
 }
 
+void launchReset(Launcher &L)
+{
+    cudaMemsetAsync(L.S.resetCount, 0, sizeof(int), L.st);
+    k_reset<<<L.gWorld(128), 128, 0, L.st>>>(L.S); L.mark("k_reset");
+    k_reset_worlds<<<dim3((L.N() * kResetSpread + 63) / 64), 64, 0, L.st>>>(L.S); L.mark("k_reset_worlds");
+}
+
 // Step task graph (src/sim.cpp:1307-1313), node order of SURVEY.md §3.3
 void launchStep(Launcher &L, float cosThr, bool nearestFirst)
 {
@@ -434,7 +443,7 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
     if (nearestFirst) k_rewards<true><<<(L.N() + kRewardWarps * kRewardWorldsPerWarp - 1) / (kRewardWarps * kRewardWorldsPerWarp), kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
     else k_rewards<false><<<(L.N() + kRewardWarps * kRewardWorldsPerWarp - 1) / (kRewardWarps * kRewardWorldsPerWarp), kRewardWarps * 32, 0, L.st>>>(L.S, cosThr);
     L.mark("k_rewards");
-    k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_reset");
+    launchReset(L);
     launchBroadphaseSetup(L, true, (L.S.p.simFlags & FLAG_ZERO_AGENT_VEL) == 0);
     launchObservations(L, cosThr, nearestFirst);
 }
@@ -448,7 +457,7 @@ extern "C" int hs_init(hs_sim *sim, void *stream)
     Launcher L{sim->S, (cudaStream_t)stream};
     k_world_init<<<L.gWorld(), 128, 0, L.st>>>(L.S);
     // Init task graph (src/sim.cpp:1295-1305): reset -> broadphase setup -> observations
-    k_reset<<<L.gWorld(64), 64, 0, L.st>>>(L.S);
+    launchReset(L);
     launchBroadphaseSetup(L, true);
     launchObservations(L, sim->cosThreshold, sim->raysNearestFirst);
     HS_CUDA(cudaGetLastError());

@@ -191,6 +191,8 @@ struct DeviceState {
     uint32_t *jmeta;         // [kMaxAgents][N]
     uint32_t *bvh;           // [N][kBvhWords]
     uint8_t *dfsLeaf;        // [N][kDfsStride] leaf ids in BVH visiting order (set by the rebuild)
+    uint32_t *resetList;     // [N] worlds to regenerate this step: world | level << 24 (compacted)
+    int *resetCount;         // [N] element 0 of a slice's view counts that slice's list
     uint16_t *cand;          // [N][kMaxCand]  a | b<<8
     float *contact;          // [N][kMaxCand][kContactWords]
     uint32_t *cmeta;         // [N][kMaxCand]
@@ -232,6 +234,7 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
     V.body += b * kMaxBodies * kBodyWords; V.meta += b * kMaxBodies; V.wi += b; V.wb += b; V.joint += b; V.jmeta += b;
     V.bvh += b * kBvhWords;
     V.dfsLeaf += b * kDfsStride;
+    V.resetList += b; V.resetCount += b;
     V.cand += b * kMaxCand;
     V.contact += b * kMaxCand * kContactWords;
     V.cmeta += b * kMaxCand;
