@@ -639,6 +639,7 @@ __global__ void k_reset(DeviceState S)
 // removes that serialisation; when most worlds reset the dense mapping issues fewer
 // instructions in total and the GPU is full anyway.
 constexpr int kResetSpread = 32;
+static_assert(kResetSpread >= 4, "the launch covers N * kResetSpread / 4 threads");
 
 __global__ void k_reset_worlds(DeviceState S)
 {

@@ -415,7 +415,8 @@ void launchReset(Launcher &L)
 {
     cudaMemsetAsync(L.S.resetCount, 0, sizeof(int), L.st);
     k_reset<<<L.gWorld(128), 128, 0, L.st>>>(L.S); L.mark("k_reset");
-    k_reset_worlds<<<dim3((L.N() * kResetSpread + 63) / 64), 64, 0, L.st>>>(L.S); L.mark("k_reset_worlds");
+    // sparse mode serves at most N/4 worlds with kResetSpread threads each; dense mode needs N threads
+    k_reset_worlds<<<dim3((L.N() * (kResetSpread / 4) + 63) / 64), 64, 0, L.st>>>(L.S); L.mark("k_reset_worlds");
 }
 
 // Step task graph (src/sim.cpp:1307-1313), node order of SURVEY.md §3.3
