@@ -517,4 +517,125 @@ __global__ void __launch_bounds__(kRewardWarps * 32) k_rewards(DeviceState S, fl
     }
 }
 
+// actionSystem (src/sim.cpp:270-370).  Lock and grab mutate shared body state and the entity-id
+// pool, so the agents of a world are processed in interface order by ONE lane; but the ray both
+// actions cast (same origin, direction and reach) only depends on the geometry, which no action
+// changes, so the rays of all agents are traced first, one lane per agent, 4 worlds per warp.
+constexpr int kActLanes = 8, kActWarps = 4;
+static_assert(kMaxAgents <= kActLanes, "one lane per agent interface");
+
+template <bool kNearestFirst>
+__global__ void __launch_bounds__(kActWarps * 32) k_action(DeviceState S)
+{
+    __shared__ AssetTable s_assets;
+    __shared__ int s_hit[kActWarps * 32];
+    __shared__ float s_t[kActWarps * 32];
+    {
+        const uint32_t *ca = reinterpret_cast<const uint32_t *>(&c_assets);
+        uint32_t *sa = reinterpret_cast<uint32_t *>(&s_assets);
+        for (int i = threadIdx.x; i < int(sizeof(AssetTable) / 4); i += blockDim.x) sa[i] = ca[i];
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int grp = lane / kActLanes, lg = lane % kActLanes;
+    const int w = (blockIdx.x * kActWarps + (threadIdx.x >> 5)) * (32 / kActLanes) + grp;
+    const bool valid = w < S.p.numWorlds;
+    const int wc = valid ? w : 0;                  // every lane joins the warp votes of the query
+    const int A = S.p.agentsPerWorld;
+    const int nDyn = WI(S, WF_NUM_DYN, wc);
+
+    bool need = false;
+    int skip = -1;
+    Vec3 ro = {0.f, 0.f, 0.f}, rd = {0.f, 1.f, 0.f};
+    if (valid && lg < A) {
+        const int slot = WB(S, WB_IFACE_SLOT + lg, w);
+        if (slot != 0xFF && !agentFrozen(S, w, WB(S, WB_IFACE_TYPE + lg, w))) {
+            const int32_t *act = S.exAction + (size_t(w) * A + lg) * 5;
+            const bool lock = act[4] == 1;
+            const bool grab = act[3] == 1 && JMETA(S, slot - nDyn, w) == 0xFFFFFFFFu;   // else: release
+            if (lock || grab) {
+                need = true;
+                const Pose p = loadPose(S, REC_POSE, slot, w);
+                ro = p.x + 0.5f * v3(0, 0, 1);
+                rd = rotate(p.q, v3(0, 1, 0));
+                skip = metaLeaf(META(S, slot, w));
+                if (!originInsideLeaf(BVH(S, w), s_assets, skip, ro)) skip = -1;
+            }
+        }
+    }
+    float t = 0.f;
+    int hit = -1;
+    if (__any_sync(0xFFFFFFFFu, need))       // warp-uniform: no lock / grab in these 4 worlds, no query
+        hit = traceRaySel<kNearestFirst>(BVH(S, wc), s_assets, need, ro, rd, 2.5f, &t, skip);
+    s_hit[threadIdx.x] = need ? hit : -1;
+    s_t[threadIdx.x] = t;
+    __syncwarp();
+    if (!valid || lg != 0) return;
+
+    const int base = threadIdx.x;          // lane 0 of the group: agent k's ray is at base + k
+    for (int k = 0; k < A; k++) {
+        int slot = WB(S, WB_IFACE_SLOT + k, w);
+        if (slot == 0xFF) continue;
+        int type = WB(S, WB_IFACE_TYPE + k, w);
+        if (agentFrozen(S, w, type)) continue;
+        int32_t *act = S.exAction + (size_t(w) * A + k) * 5;
+        const int hitK = s_hit[base + k];
+        const float tK = s_t[base + k];
+
+        if (act[4] == 1 && hitK >= 0) {
+            uint32_t m = META(S, hitK, w);
+            int owner = metaOwner(m), resp = metaResp(m);
+            if (resp == RESP_STATIC) {
+                if ((type == AGENT_SEEKER && owner == OWNER_SEEKER) ||
+                    (type == AGENT_HIDER && owner == OWNER_HIDER)) {
+                    resp = RESP_DYNAMIC; owner = OWNER_NONE;
+                }
+            } else if (owner == OWNER_NONE) {
+                resp = RESP_STATIC;
+                owner = type == AGENT_HIDER ? OWNER_HIDER : OWNER_SEEKER;
+            }
+            META(S, hitK, w) = packMeta(metaObj(m), resp, owner, metaEid(m), metaLeaf(m));
+        }
+
+        if (act[3] == 1) {
+            int ak = slot - nDyn;       // DynAgent row
+            uint32_t jm = JMETA(S, ak, w);
+            if (jm != 0xFFFFFFFFu) {
+                IdPool ids(S, w);
+                ids.release((jm >> 8) & 0xFF);
+                ids.commit();
+                JMETA(S, ak, w) = 0xFFFFFFFFu;
+            } else if (hitK >= 0) {
+                uint32_t m = META(S, hitK, w);
+                if (metaOwner(m) == OWNER_NONE && metaResp(m) == RESP_DYNAMIC) {
+                    const Pose p = loadPose(S, REC_POSE, slot, w);
+                    Vec3 rok = p.x + 0.5f * v3(0, 0, 1);
+                    Vec3 rdk = rotate(p.q, v3(0, 1, 0));
+                    Vec3 opos = loadPos(S, hitK, w);
+                    Quat orot = loadRot(S, hitK, w);
+                    Vec3 r1 = 1.25f * v3(0, 1, 0) + 0.5f * v3(0, 0, 1);
+                    Vec3 hitPos = rok + rdk * tK;
+                    Vec3 r2 = rotate(qinv(orot), hitPos - opos);
+                    Quat a2 = qnormalize(qinv(orot) * p.q);
+                    IdPool ids(S, w);
+                    int eid = ids.acquire();
+                    ids.commit();
+                    int seq = WI(S, WF_JOINT_SEQ, w);
+                    WI(S, WF_JOINT_SEQ, w) = seq + 1;
+                    JMETA(S, ak, w) = (uint32_t(seq & 0xFFFF) << 16) | (uint32_t(eid) << 8) | uint32_t(hitK);
+                    JF(S, JF_A1W, ak, w) = 1.f; JF(S, JF_A1X, ak, w) = 0.f;
+                    JF(S, JF_A1Y, ak, w) = 0.f; JF(S, JF_A1Z, ak, w) = 0.f;
+                    JF(S, JF_A2W, ak, w) = a2.w; JF(S, JF_A2X, ak, w) = a2.x;
+                    JF(S, JF_A2Y, ak, w) = a2.y; JF(S, JF_A2Z, ak, w) = a2.z;
+                    JF(S, JF_SEP, ak, w) = tK - 1.25f;
+                    JF(S, JF_R1X, ak, w) = r1.x; JF(S, JF_R1Y, ak, w) = r1.y; JF(S, JF_R1Z, ak, w) = r1.z;
+                    JF(S, JF_R2X, ak, w) = r2.x; JF(S, JF_R2Y, ak, w) = r2.y; JF(S, JF_R2Z, ak, w) = r2.z;
+                }
+            }
+        }
+
+        act[0] = 2; act[1] = 2; act[2] = 2; act[3] = 0; act[4] = 0;
+    }
+}
+
 }  // namespace hs

@@ -424,7 +424,12 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
 {
     k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.mark("k_move");
     launchBroadphaseSetup(L, false);       // a rebuild is only ever pending right after a reset
-    k_action<<<L.gWorld(64), 64, 0, L.st>>>(L.S); L.mark("k_action");
+    {
+        const unsigned nb = unsigned((L.N() + kActWarps * (32 / kActLanes) - 1) / (kActWarps * (32 / kActLanes)));
+        if (nearestFirst) k_action<true><<<nb, kActWarps * 32, 0, L.st>>>(L.S);
+        else k_action<false><<<nb, kActWarps * 32, 0, L.st>>>(L.S);
+        L.mark("k_action");
+    }
     k_broadphase<<<(L.N() + kBroadWarps - 1) / kBroadWarps, kBroadWarps * 32, 0, L.st>>>(L.S); L.mark("k_broadphase");
     for (int i = 0; i < kSubsteps; i++) {
         k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep");
