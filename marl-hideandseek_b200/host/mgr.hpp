@@ -26,24 +26,18 @@ namespace GPUHideSeek {
 
 class Manager {
 public:
-    struct Config {
-        madrona::ExecMode execMode;
-        int gpuID;
-        uint32_t numWorlds;
-        SimFlags simFlags;
-        uint32_t randSeed;
-        uint32_t minHiders;
-        uint32_t maxHiders;
-        uint32_t minSeekers;
-        uint32_t maxSeekers;
-        uint32_t numPBTPolicies;
+    using Tensor = madrona::py::Tensor;      // non-owning device tensor descriptor
+    using CountT = madrona::CountT;
+
+    struct Config {      // same members, types and order as the reference's Manager::Config
+        madrona::ExecMode execMode;  int gpuID;  uint32_t numWorlds;  SimFlags simFlags;  uint32_t randSeed;
+        uint32_t minHiders, maxHiders, minSeekers, maxSeekers, numPBTPolicies;
         bool enableBatchRenderer;
-        uint32_t batchRenderViewWidth = 64;
-        uint32_t batchRenderViewHeight = 64;
-        madrona::render::APIBackend *extRenderAPI = nullptr;
-        madrona::render::GPUDevice *extRenderDev = nullptr;
+        uint32_t batchRenderViewWidth = 64, batchRenderViewHeight = 64;
+        madrona::render::APIBackend *extRenderAPI = nullptr;  madrona::render::GPUDevice *extRenderDev = nullptr;
         uint32_t worldBase = 0;      // extension: first global world index of this shard
     };
+
 
     Manager(const Config &cfg);
     ~Manager();
@@ -53,8 +47,8 @@ public:
     void init();
     void step();     // synchronous, like the reference's graph launch + stream sync
 
-    void saveCheckpoint(madrona::CountT world_idx);
-    void loadCheckpoint(madrona::CountT world_idx);
+    void saveCheckpoint(CountT world_idx);
+    void loadCheckpoint(CountT world_idx);
     void loadCheckpoints();
 
     // XLA custom-call bodies (src/mgr.hpp:44-50, src/mgr.cpp:365-437): `buffers` = device
@@ -65,38 +59,38 @@ public:
     void gpuJAXSaveCheckpoints(cudaStream_t strm, void **buffers);
     void gpuJAXLoadCheckpoints(cudaStream_t strm, void **buffers);
 
-    madrona::py::Tensor resetTensor() const;
-    madrona::py::Tensor doneTensor() const;
-    madrona::py::Tensor prepCounterTensor() const;
-    madrona::py::Tensor actionTensor() const;
-    madrona::py::Tensor rewardTensor() const;
-    madrona::py::Tensor selfDataTensor() const;
-    madrona::py::Tensor selfTypeTensor() const;
-    madrona::py::Tensor selfMaskTensor() const;
-    madrona::py::Tensor agentDataTensor() const;
-    madrona::py::Tensor boxDataTensor() const;
-    madrona::py::Tensor rampDataTensor() const;
-    madrona::py::Tensor visibleAgentsMaskTensor() const;
-    madrona::py::Tensor visibleBoxesMaskTensor() const;
-    madrona::py::Tensor visibleRampsMaskTensor() const;
-    madrona::py::Tensor globalPositionsTensor() const;
-    madrona::py::Tensor lidarTensor() const;
-    madrona::py::Tensor seedTensor() const;
+    Tensor resetTensor() const;
+    Tensor doneTensor() const;
+    Tensor prepCounterTensor() const;
+    Tensor actionTensor() const;
+    Tensor rewardTensor() const;
+    Tensor selfDataTensor() const;
+    Tensor selfTypeTensor() const;
+    Tensor selfMaskTensor() const;
+    Tensor agentDataTensor() const;
+    Tensor boxDataTensor() const;
+    Tensor rampDataTensor() const;
+    Tensor visibleAgentsMaskTensor() const;
+    Tensor visibleBoxesMaskTensor() const;
+    Tensor visibleRampsMaskTensor() const;
+    Tensor globalPositionsTensor() const;
+    Tensor lidarTensor() const;
+    Tensor seedTensor() const;
 
-    madrona::py::Tensor checkpointControlTensor() const;
-    madrona::py::Tensor checkpointTensor() const;
+    Tensor checkpointControlTensor() const;
+    Tensor checkpointTensor() const;
 
-    madrona::py::Tensor depthTensor() const;
-    madrona::py::Tensor rgbTensor() const;
+    Tensor depthTensor() const;
+    Tensor rgbTensor() const;
 
-    void triggerReset(madrona::CountT world_idx, madrona::CountT level_idx);
-    void setAction(madrona::CountT agent_idx, int32_t x, int32_t y, int32_t r, bool g, bool l);
+    void triggerReset(CountT world_idx, CountT level_idx);
+    void setAction(CountT agent_idx, int32_t x, int32_t y, int32_t r, bool g, bool l);
 
     madrona::render::RenderManager &getRenderManager();
 
-    madrona::py::Tensor policyAssignmentsTensor() const;
-    madrona::py::Tensor episodeResultTensor() const;
-    madrona::py::Tensor simControlTensor() const;       // empty, as in the reference
+    Tensor policyAssignmentsTensor() const;
+    Tensor episodeResultTensor() const;
+    Tensor simControlTensor() const;       // empty, as in the reference
 
     madrona::py::TrainInterface trainInterface() const;
 
