@@ -46,7 +46,10 @@ enum hs_export_id {
     HS_EXPORT_RAMP_OBS, HS_EXPORT_AGENT_VIS, HS_EXPORT_BOX_VIS, HS_EXPORT_RAMP_VIS,
     HS_EXPORT_LIDAR, HS_EXPORT_SEED, HS_EXPORT_REWARD, HS_EXPORT_DONE,
     HS_EXPORT_GLOBAL_POS, HS_EXPORT_AGENT_POLICY, HS_EXPORT_EPISODE_RESULT,
-    HS_EXPORT_CKPT_CTRL, HS_EXPORT_CKPT, HS_NUM_EXPORTS
+    HS_EXPORT_CKPT_CTRL, HS_EXPORT_CKPT, HS_NUM_EXPORTS,
+    /* not ExportIDs in the reference (they come from its render manager,
+     * src/mgr.cpp:1241-1263); valid after hs_enable_views */
+    HS_EXPORT_VIEW_DEPTH = HS_NUM_EXPORTS, HS_EXPORT_VIEW_RGB
 };
 
 /* TensorElementType subset (M/include/madrona/py/utils.hpp) */
@@ -117,6 +120,24 @@ void hs_xla_gpu_init(void *stream, void **buffers, const char *opaque, size_t op
 void hs_xla_gpu_step(void *stream, void **buffers, const char *opaque, size_t opaque_len);
 void hs_xla_gpu_save_checkpoints(void *stream, void **buffers, const char *opaque, size_t opaque_len);
 void hs_xla_gpu_load_checkpoints(void *stream, void **buffers, const char *opaque, size_t opaque_len);
+
+/* Agent camera views = the batch renderer's outputs (Config::enableBatchRenderer,
+ * batchRenderViewWidth/Height, src/mgr.hpp:27-29; RenderManager::batchRender after init and
+ * every step, src/mgr.cpp:876-880, 898-902; depthTensor / rgbTensor, src/mgr.cpp:1241-1263).
+ * The Vulkan rasteriser is unavailable here; this is a CUDA ray caster with the arithmetic of
+ * Madrona's software ray caster (M/src/mw/device/bvh_raycast.cpp) — see csrc/hs_views.cuh.
+ *   hs_enable_views: call once between hs_create and hs_init.  `data_dir` = the reference's
+ *     data/ directory (render OBJ meshes, src/mgr.cpp:590-609); NULL/"" = $HIDESEEK_DATA_DIR,
+ *     else built-in meshes.  Allocates [N*A,H,W,1] f32 depth and [N*A,H,W,4] u8 RGBA.
+ *   hs_render_views: renders every agent slot's view of the current state on `stream`
+ *     (asynchronous); the Manager calls it after hs_init / hs_step like the reference.
+ *   hs_export(HS_EXPORT_VIEW_DEPTH / HS_EXPORT_VIEW_RGB) returns the two tensors.
+ *   hs_build_view_mesh_table: parity/diagnostic, host only — the render-mesh table
+ *     (hs::ViewMeshTable, csrc/hs_views.cuh) hs_enable_views builds for `data_dir`. */
+int hs_enable_views(hs_sim *sim, int width, int height, const char *data_dir);
+int hs_render_views(hs_sim *sim, void *stream);
+int hs_view_mesh_table_bytes(void);
+int hs_build_view_mesh_table(const char *data_dir, void *out, int out_bytes);
 
 /* Diagnostics / parity: flat per-world internal state (layout in
  * hideseek/debug_dump.h), number of kernels launched by the last hs_step,

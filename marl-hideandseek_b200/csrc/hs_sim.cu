@@ -25,6 +25,7 @@
 #include "hs_narrowphase.cuh"
 #include "hs_solver.cuh"
 #include "hs_checkpoint.cuh"
+#include "hs_views.cuh"
 
 namespace hs {
 void buildAssetTable(AssetTable &T);
@@ -58,6 +59,10 @@ struct hs_sim {
     bool obsFork = true;
     bool inited = false;
     float cosThreshold = 0.f;
+    // agent camera views (hs_views.cuh); off unless hs_enable_views was called
+    bool viewsEnabled = false;
+    ViewParams view{};
+    ViewMeshTable *viewMeshHost = nullptr;
 };
 
 template <typename T>
@@ -217,6 +222,7 @@ extern "C" void hs_destroy(hs_sim *sim)
         if (sim->joinEvent[b]) cudaEventDestroy(sim->joinEvent[b]);
     }
     for (void *p : sim->allocs) cudaFree(p);
+    delete sim->viewMeshHost;
     delete sim;
 }
 
@@ -471,6 +477,53 @@ extern "C" int hs_init(hs_sim *sim, void *stream)
     return 0;
 }
 
+// ---- agent camera views (batch renderer outputs, src/mgr.cpp:876-880, 1241-1263) ---------------
+extern "C" int hs_enable_views(hs_sim *sim, int width, int height, const char *data_dir)
+{
+    if (!sim) { g_err = "hs_enable_views: null sim"; return 1; }
+    if (sim->viewsEnabled) { g_err = "hs_enable_views: already enabled"; return 1; }
+    if (width <= 0 || height <= 0 || width > 4096 || height > 4096) { g_err = "hs_enable_views: invalid view size"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    if (!data_dir || !data_dir[0]) data_dir = getenv("HIDESEEK_DATA_DIR");
+    sim->viewMeshHost = new ViewMeshTable();
+    const char *err = buildViewMeshTable(*sim->viewMeshHost, data_dir);
+    if (err[0]) { g_err = std::string("hs_enable_views: ") + err; return 1; }
+    ViewMeshTable *dev = nullptr;
+    HS_TRY(devAlloc(sim, &dev, 1));
+    HS_CUDA(cudaMemcpy(dev, sim->viewMeshHost, sizeof(ViewMeshTable), cudaMemcpyHostToDevice));
+    const size_t pixels = size_t(sim->cfg.num_worlds) * sim->S.p.agentsPerWorld * width * height;
+    HS_TRY(devAlloc(sim, &sim->view.depth, pixels));
+    HS_TRY(devAlloc(sim, &sim->view.rgb, pixels * 4));
+    sim->view.mesh = dev;
+    sim->view.width = width;
+    sim->view.height = height;
+    sim->viewsEnabled = true;
+    return 0;
+}
+
+extern "C" int hs_render_views(hs_sim *sim, void *stream)
+{
+    if (!sim || !sim->inited) { g_err = "hs_render_views: hs_init has not run"; return 1; }
+    if (!sim->viewsEnabled) { g_err = "hs_render_views: agent views are not enabled (hs_enable_views)"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    const unsigned views = unsigned(sim->cfg.num_worlds) * sim->S.p.agentsPerWorld;
+    k_agent_views<<<views, kViewThreads, 0, (cudaStream_t)stream>>>(sim->S, sim->view);
+    HS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int hs_view_mesh_table_bytes(void) { return (int)sizeof(ViewMeshTable); }
+
+// host-only: the table hs_enable_views would build for `data_dir` (no device needed)
+extern "C" int hs_build_view_mesh_table(const char *data_dir, void *out, int out_bytes)
+{
+    if (!out || out_bytes != (int)sizeof(ViewMeshTable)) { g_err = "hs_build_view_mesh_table: bad buffer"; return 1; }
+    if (!data_dir || !data_dir[0]) data_dir = getenv("HIDESEEK_DATA_DIR");
+    const char *err = buildViewMeshTable(*(ViewMeshTable *)out, data_dir);
+    if (err[0]) { g_err = std::string("hs_build_view_mesh_table: ") + err; return 1; }
+    return 0;
+}
+
 extern "C" int hs_sync(hs_sim *sim, void *stream)
 {
     HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
@@ -509,6 +562,14 @@ extern "C" int hs_export(hs_sim *sim, int id, void **ptr, int *dtype, int *ndim,
     case HS_EXPORT_EPISODE_RESULT: set(S.exEpisodeResult, HS_F32, 2, N, 2, 0); break;
     case HS_EXPORT_CKPT_CTRL: set(S.exCkptCtrl, HS_I32, 2, N, 1, 0); break;
     case HS_EXPORT_CKPT: set(S.exCkpt, HS_U8, 2, N, kCheckpointBytes, 0); break;
+    // renderer outputs (src/mgr.cpp:1241-1263): [N*A, H, W, 1] f32 and [N*A, H, W, 4] u8
+    case HS_EXPORT_VIEW_DEPTH:
+    case HS_EXPORT_VIEW_RGB:
+        if (!sim->viewsEnabled) { g_err = "hs_export: agent views are not enabled (hs_enable_views)"; return 1; }
+        if (id == HS_EXPORT_VIEW_DEPTH) set(sim->view.depth, HS_F32, 4, R, sim->view.height, sim->view.width);
+        else set(sim->view.rgb, HS_U8, 4, R, sim->view.height, sim->view.width);
+        dims[3] = id == HS_EXPORT_VIEW_DEPTH ? 1 : 4;
+        break;
     default: g_err = "hs_export: unknown export id"; return 1;
     }
     return 0;

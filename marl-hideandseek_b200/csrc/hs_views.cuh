@@ -1,0 +1,251 @@
+// Agent camera views: per-agent depth + RGB images ray-cast over the world's render instances.
+//
+// Replaces the reference's batch renderer output (Manager::depthTensor / rgbTensor,
+// src/mgr.cpp:1241-1263) with a CUDA ray caster that follows the arithmetic of Madrona's
+// software ray caster (M/src/mw/device/bvh_raycast.cpp):
+//   * camera: entity position + 0.5*up, entity rotation, vertical fov 100 deg
+//     (src/sim.cpp:1399-1403; viewTransformUpdate M/src/render/ecs_system.cpp:274-313);
+//   * primary ray per pixel: calculateOutRay (bvh_raycast.cpp:58-88);
+//   * per instance the ray is moved into object space, re-normalised, and tested against the
+//     render mesh with the watertight test of Woop et al. with back-face culling
+//     (bvh_raycast.cpp:228-270, 317-447, 614-633; MADRONA_MESHBVH_BACKFACE_CULLING is defined
+//     in M/include/madrona/mesh_bvh.inl:3);
+//   * depth = distance along the unit ray to the closest hit, 0 on a miss; this environment
+//     creates no light entities, so computeFragment's colour is max(0.2, 0) * material colour
+//     (bvh_raycast.cpp:848-935); rgb bytes = colour * 255 truncated, alpha 255 (:822-839).
+// What differs by design: no TLAS/BLAS walk — a world has <= 52 instances, so a CTA stages
+// their object-space transforms and world AABBs in shared memory once per view and every
+// pixel runs one uniform loop over them (slab cull, then the mesh's triangle clusters).
+// Texture lookups (plane grid, agent faces) are not reproduced: textured materials use their
+// base colour.  Inactive agent slots produce an all-zero view.
+#pragma once
+
+#include "hs_state.cuh"
+
+namespace hs {
+
+constexpr int kViewMaxTris = 1600;
+constexpr int kViewMaxClusters = 160;
+constexpr int kViewMaxSubmeshes = 16;
+constexpr int kViewMaxSubPerObj = 3;
+constexpr int kViewClusterTris = 16;
+constexpr int kViewThreads = 256;
+
+struct ViewBox { float lo[3]; int first; float hi[3]; int count; };     // 32 B
+struct ViewMeshTable {
+    int objFirstSub[OBJ_COUNT], objNumSub[OBJ_COUNT];
+    float objAabb[OBJ_COUNT][6];
+    float subColor[OBJ_COUNT][kViewMaxSubPerObj][3];   // material base colour of (object, submesh)
+    ViewBox sub[kViewMaxSubmeshes];                    // first/count index clusters
+    ViewBox cluster[kViewMaxClusters];                 // first/count index triangles
+    int numSub, numClusters, numTris, pad;
+    float fovScale;                                    // 1 / tanf(toRadians(100 / 2))
+    float tri[kViewMaxTris][9];                        // a, b, c in object space
+};
+
+struct ViewParams {
+    const ViewMeshTable *mesh;
+    float *depth;            // [N*A, H, W, 1]
+    uint8_t *rgb;            // [N*A, H, W, 4]
+    int width, height;
+};
+
+#if defined(__CUDACC__) && !defined(HS_VIEWS_HOST_ONLY)
+
+struct ViewInst {
+    Vec3 lo, hi;             // world AABB of the instance's render mesh
+    Vec3 ro;                 // camera origin in object space
+    Quat qinv;
+    Vec3 invS;
+    int obj;
+};
+
+struct ViewSmem {
+    ViewInst inst[kMaxBodies];
+    int numInst;
+    int active;
+    Vec3 origin, lowerLeft, horizontal, vertical;
+};
+
+struct WoopRay { int kx, ky, kz; float Sx, Sy, Sz; };
+
+// computeRayIsectInfo (bvh_raycast.cpp:228-270)
+__device__ __forceinline__ WoopRay woopSetup(Vec3 d)
+{
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    int kz = (ax > ay && ax > az) ? 0 : (ay > az ? 1 : 2);
+    int kx = kz + 1; if (kx == 3) kx = 0;
+    int ky = kx + 1; if (ky == 3) ky = 0;
+    float dz = comp(d, kz);
+    if (dz < 0.f) { int t = kx; kx = ky; ky = t; }
+    float inv = 1.f / dz;
+    return {kx, ky, kz, comp(d, kx) * inv, comp(d, ky) * inv, inv};
+}
+
+// rayTriangleIntersection with back-face culling (bvh_raycast.cpp:317-447); returns the hit
+// distance in object-space units of the normalised ray, or a negative value on a miss.
+__device__ __forceinline__ float woopHit(const float *t9, const WoopRay &R, Vec3 org, float t_max)
+{
+    Vec3 A = {t9[0] - org.x, t9[1] - org.y, t9[2] - org.z};
+    Vec3 B = {t9[3] - org.x, t9[4] - org.y, t9[5] - org.z};
+    Vec3 C = {t9[6] - org.x, t9[7] - org.y, t9[8] - org.z};
+    float a_kz = comp(A, R.kz), a_kx = comp(A, R.kx), a_ky = comp(A, R.ky);
+    float b_kz = comp(B, R.kz), b_kx = comp(B, R.kx), b_ky = comp(B, R.ky);
+    float c_kz = comp(C, R.kz), c_kx = comp(C, R.kx), c_ky = comp(C, R.ky);
+    float Ax = fmaf(-R.Sx, a_kz, a_kx), Ay = fmaf(-R.Sy, a_kz, a_ky);
+    float Bx = fmaf(-R.Sx, b_kz, b_kx), By = fmaf(-R.Sy, b_kz, b_ky);
+    float Cx = fmaf(-R.Sx, c_kz, c_kx), Cy = fmaf(-R.Sy, c_kz, c_ky);
+    float U = fmaf(Cx, By, -Cy * Bx);
+    float V = fmaf(Ax, Cy, -Ay * Cx);
+    float W = fmaf(Bx, Ay, -By * Ax);
+    const float eps = 1e-7f;
+    if (U > -eps && U < eps) U = 0.f;
+    if (V > -eps && V < eps) V = 0.f;
+    if (W > -eps && W < eps) W = 0.f;
+    if (U < 0.f || V < 0.f || W < 0.f) return -1.f;
+    if (U == 0.f || V == 0.f || W == 0.f) {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+        if (U < 0.f || V < 0.f || W < 0.f) return -1.f;
+    }
+    float det = U + V + W;
+    if (det == 0.f) return -1.f;
+    float Az = R.Sz * a_kz, Bz = R.Sz * b_kz, Cz = R.Sz * c_kz;
+    float T = fmaf(U, Az, fmaf(V, Bz, W * Cz));
+    if (T < 0.f || T > t_max * det) return -1.f;
+    return T * (1.f / det);
+}
+
+__device__ __forceinline__ bool viewSlab(const float *lo, const float *hi, Vec3 o, Vec3 inv_d, float t_max)
+{
+    return aabbRayIntersects({lo[0], lo[1], lo[2]}, {hi[0], hi[1], hi[2]}, o, inv_d, 0.f, t_max);
+}
+
+// One CTA per view (world, agent slot); a warp shades 8x4 pixel tiles.
+__global__ void __launch_bounds__(kViewThreads) k_agent_views(DeviceState S, ViewParams P)
+{
+    __shared__ ViewSmem sm;
+    const int A = S.p.agentsPerWorld;
+    const int view = blockIdx.x;
+    const int w = view / A, k = view - w * A;
+    const int W = P.width, H = P.height;
+    const ViewMeshTable &M = *P.mesh;
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+        int slot = WB(S, WB_IFACE_SLOT + k, w);
+        sm.active = slot != 0xFF;
+        sm.numInst = WI(S, WF_NUM_BODIES, w);
+        if (sm.active) {
+            // viewTransformUpdate + calculateOutRay
+            Pose ps = loadPose(S, REC_POSE, slot, w);
+            Vec3 start = ps.x + v3(0.f, 0.f, 0.5f);
+            Vec3 forward = normalize(rotate(ps.q, v3(0.f, 1.f, 0.f)));
+            Vec3 u = rotate(ps.q, v3(1.f, 0.f, 0.f));
+            Vec3 v = normalize(cross(forward, u));
+            float h = 1.f / M.fovScale;
+            float vp = 2.f * h;
+            sm.horizontal = u * vp;
+            sm.vertical = v * vp;
+            sm.origin = start;
+            sm.lowerLeft = start - sm.horizontal / 2.f - sm.vertical / 2.f + forward;
+        }
+    }
+    __syncthreads();
+    const size_t pixBase = size_t(view) * W * H;
+    if (!sm.active) {
+        for (int i = tid; i < W * H; i += kViewThreads) {
+            P.depth[pixBase + i] = 0.f;
+            reinterpret_cast<uint32_t *>(P.rgb)[pixBase + i] = 0u;
+        }
+        return;
+    }
+    const int nInst = sm.numInst;
+    if (tid < nInst) {
+        ViewInst I;
+        uint32_t m = META(S, tid, w);
+        I.obj = metaObj(m);
+        Pose ps = loadPose(S, REC_POSE, tid, w);
+        Vec3 sc = loadScale(S, tid, w);
+        // instanceHasVolume (bvh_raycast.cpp:272-277) and meshes this table does not carry
+        bool skip = (sc.x == 0.f && sc.y == 0.f && sc.z == 0.f) || M.objNumSub[I.obj] == 0;
+        if (skip) I.obj = -1;
+        const float *bb = M.objAabb[I.obj < 0 ? 0 : I.obj];
+        AABB wb = aabbApplyTRS({{bb[0], bb[1], bb[2]}, {bb[3], bb[4], bb[5]}}, ps.x, ps.q, sc);
+        // the cull must never reject a ray the triangle test would accept: pad by rounding slack
+        Vec3 ext = (wb.hi - wb.lo) * 1e-5f + v3(1e-5f, 1e-5f, 1e-5f);
+        I.lo = wb.lo - ext; I.hi = wb.hi + ext;
+        I.qinv = qinv(ps.q);
+        I.invS = {1.f / sc.x, 1.f / sc.y, 1.f / sc.z};
+        I.ro = mulDiag(I.invS, rotate(I.qinv, sm.origin - ps.x));
+        sm.inst[tid] = I;
+    }
+    __syncthreads();
+
+    const int warp = tid >> 5, lane = tid & 31;
+    const int tilesX = (W + 7) / 8, tilesY = (H + 3) / 4;
+    const Vec3 o = sm.origin;
+    for (int tile = warp; tile < tilesX * tilesY; tile += kViewThreads / 32) {
+        const int px = (tile % tilesX) * 8 + (lane & 7);
+        const int py = (tile / tilesX) * 4 + (lane >> 3);
+        if (px >= W || py >= H) continue;
+        float pu = (float(px) + 0.5f) / float(W);
+        float pv = (float(py) + 0.5f) / float(H);
+        Vec3 d = normalize(sm.lowerLeft + pu * sm.horizontal + pv * sm.vertical - o);
+        Vec3 invd = {1.f / d.x, 1.f / d.y, 1.f / d.z};
+        float best = 10000.f;
+        int hitObj = -1, hitSub = 0;
+        for (int i = 0; i < nInst; i++) {
+            const ViewInst &I = sm.inst[i];
+            if (I.obj < 0) continue;
+            if (!aabbRayIntersects(I.lo, I.hi, o, invd, 0.f, best)) continue;
+            Vec3 rd = mulDiag(I.invS, rotate(I.qinv, d));
+            float ts = length(rd);
+            rd = rd / ts;
+            Vec3 ro = I.ro;
+            float tmax = best * ts;
+            WoopRay R = woopSetup(rd);
+            Vec3 invrd = {1.f / rd.x, 1.f / rd.y, 1.f / rd.z};
+            bool hit = false;
+            const int s0 = M.objFirstSub[I.obj], ns = M.objNumSub[I.obj];
+            for (int s = 0; s < ns; s++) {
+                const ViewBox &SB = M.sub[s0 + s];
+                if (ns > 1 && !viewSlab(SB.lo, SB.hi, ro, invrd, tmax)) continue;
+                for (int c = 0; c < SB.count; c++) {
+                    const ViewBox &CB = M.cluster[SB.first + c];
+                    if (SB.count > 1 && !viewSlab(CB.lo, CB.hi, ro, invrd, tmax)) continue;
+                    for (int t = 0; t < CB.count; t++) {
+                        float th = woopHit(M.tri[CB.first + t], R, ro, tmax);
+                        if (th >= 0.f) { tmax = th; hit = true; hitSub = s; }
+                    }
+                }
+            }
+            if (hit) { best = tmax / ts; hitObj = I.obj; }
+        }
+        const size_t pix = pixBase + size_t(py) * W + px;
+        uint32_t rgba = 0xFF000000u;
+        float depth = 0.f;
+        if (hitObj >= 0) {
+            depth = best;
+            const float *col = M.subColor[hitObj][hitSub];
+            // acc_color = fmaxf(0.2, light_contrib = 0) * color, clamped to 1; bytes truncate
+            uint32_t r = (uint32_t)(fminf(1.f, 0.2f * col[0]) * 255.f);
+            uint32_t g = (uint32_t)(fminf(1.f, 0.2f * col[1]) * 255.f);
+            uint32_t b = (uint32_t)(fminf(1.f, 0.2f * col[2]) * 255.f);
+            rgba |= r | (g << 8) | (b << 16);
+        }
+        P.depth[pix] = depth;
+        reinterpret_cast<uint32_t *>(P.rgb)[pix] = rgba;
+    }
+}
+
+#endif  // __CUDACC__
+
+// host side (hs_view_assets.cpp): fills the table from the reference's data directory
+// (plane.obj, cube_render.obj, wall_render.obj, agent_render.obj, ramp_render.obj,
+// elongated_render.obj — src/mgr.cpp:590-609) or, with dataDir == nullptr, from built-in
+// descriptions of the same shapes.  Returns an empty string on success, else the error.
+const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir);
+
+}  // namespace hs

@@ -83,6 +83,7 @@ def load_library():
     l.hs_profiled_kernel_name.argtypes = [C.c_int]
     l.hs_profiled_kernel_name.restype = C.c_char_p
     l.hs_world_stats.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+    l.hs_build_view_mesh_table.argtypes = [C.c_char_p, C.c_void_p, C.c_int]
     _lib = l
     return l
 
@@ -90,6 +91,17 @@ def load_library():
 def _check(rc):
     if rc != 0:
         raise RuntimeError("hideseek: " + load_library().hs_last_error().decode())
+
+
+def view_mesh_table(data_dir=None):
+    """The render-mesh table of the agent views (csrc/hs_views.cuh) as a numpy record: built-in
+    meshes, or the OBJ files of `data_dir` (the reference's data/ directory).  Host only."""
+    from .dump import view_mesh_dt
+    lib = load_library()
+    out = np.zeros(1, dtype=view_mesh_dt)
+    assert lib.hs_view_mesh_table_bytes() == view_mesh_dt.itemsize
+    _check(lib.hs_build_view_mesh_table((data_dir or "").encode(), out.ctypes.data, view_mesh_dt.itemsize))
+    return out[0]
 
 
 class HideAndSeekSimulator(_native.HideAndSeekSimulator):
@@ -103,11 +115,12 @@ class HideAndSeekSimulator(_native.HideAndSeekSimulator):
     def __init__(self, exec_mode=madrona.ExecMode.CUDA, gpu_id=0, num_worlds=1, sim_flags=0,
                  rand_seed=0, min_hiders=2, max_hiders=2, min_seekers=2, max_seekers=2,
                  num_pbt_policies=0, enable_batch_renderer=False, batch_render_width=64,
-                 batch_render_height=64, world_base=0):
+                 batch_render_height=64, world_base=0, render_data_dir=None):
         super().__init__(exec_mode, int(gpu_id), int(num_worlds), int(sim_flags), int(rand_seed),
                          int(min_hiders), int(max_hiders), int(min_seekers), int(max_seekers),
                          int(num_pbt_policies), bool(enable_batch_renderer),
-                         int(batch_render_width), int(batch_render_height), int(world_base))
+                         int(batch_render_width), int(batch_render_height), int(world_base),
+                         str(render_data_dir or ""))
         self._clib = load_library()
         self._h = C.c_void_p(self.handle())
 

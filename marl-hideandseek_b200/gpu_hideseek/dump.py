@@ -24,3 +24,11 @@ world_dt = np.dtype([
     ("leaf_slot", "i4", 52),
     ("cand_a", "i4", 256), ("cand_b", "i4", 256), ("contact_meta", "i4", 256),
     ("contacts", "f4", (256, 20))])
+
+# mirror of hs::ViewMeshTable (csrc/hs_views.cuh)
+view_box_dt = np.dtype([("lo", "f4", 3), ("first", "i4"), ("hi", "f4", 3), ("count", "i4")])
+view_mesh_dt = np.dtype([
+    ("obj_first_sub", "i4", 8), ("obj_num_sub", "i4", 8), ("obj_aabb", "f4", (8, 6)),
+    ("sub_color", "f4", (8, 3, 3)), ("sub", view_box_dt, 16), ("cluster", view_box_dt, 160),
+    ("num_sub", "i4"), ("num_clusters", "i4"), ("num_tris", "i4"), ("pad", "i4"),
+    ("fov_scale", "f4"), ("tri", "f4", (1600, 9))])

@@ -155,7 +155,7 @@ PYBIND11_MODULE(_native, m)
                          uint32_t max_hiders, uint32_t min_seekers, uint32_t max_seekers,
                          uint32_t num_pbt_policies, bool enable_batch_renderer,
                          int64_t batch_render_width, int64_t batch_render_height,
-                         int64_t world_base) {
+                         int64_t world_base, const std::string &render_data_dir) {
                  Manager::Config cfg{};
                  cfg.execMode = exec_mode;
                  cfg.gpuID = (int)gpu_id;
@@ -171,13 +171,15 @@ PYBIND11_MODULE(_native, m)
                  cfg.batchRenderViewWidth = (uint32_t)batch_render_width;
                  cfg.batchRenderViewHeight = (uint32_t)batch_render_height;
                  cfg.worldBase = (uint32_t)world_base;
+                 cfg.renderDataDir = render_data_dir.empty() ? nullptr : render_data_dir.c_str();
                  return new Manager(cfg);
              }),
              py::arg("exec_mode"), py::arg("gpu_id"), py::arg("num_worlds"), py::arg("sim_flags"),
              py::arg("rand_seed"), py::arg("min_hiders"), py::arg("max_hiders"),
              py::arg("min_seekers"), py::arg("max_seekers"), py::arg("num_pbt_policies"),
              py::arg("enable_batch_renderer") = false, py::arg("batch_render_width") = 64,
-             py::arg("batch_render_height") = 64, py::arg("world_base") = 0)
+             py::arg("batch_render_height") = 64, py::arg("world_base") = 0,
+             py::arg("render_data_dir") = std::string())
         .def("init", &Manager::init)
         .def("step", &Manager::step, py::call_guard<py::gil_scoped_release>())
         HS_TENSOR("reset_tensor", resetTensor)

@@ -45,8 +45,8 @@ Manager::Manager(const Config &cfg) : impl_(new Impl{cfg, nullptr})
 {
     if (cfg.execMode != madrona::ExecMode::CUDA)
         fatal("ExecMode::CPU requested: this build has only the CUDA (sm_100a) backend and no CPU fallback");
-    if (cfg.enableBatchRenderer || cfg.extRenderAPI || cfg.extRenderDev)
-        fatal("batch renderer requested: graphics APIs are unavailable on this box");
+    if (cfg.extRenderAPI || cfg.extRenderDev)
+        fatal("external render device requested: graphics APIs are unavailable on this box");
     hs_config c{};
     c.gpu_id = cfg.gpuID;
     c.num_worlds = (int32_t)cfg.numWorlds;
@@ -64,6 +64,11 @@ Manager::Manager(const Config &cfg) : impl_(new Impl{cfg, nullptr})
         impl_ = nullptr;
         fatal(msg);
     }
+    // initRenderManager (src/mgr.cpp:54-88): the batch renderer's per-agent views are ray-cast
+    // in CUDA (hs_enable_views), not rasterised through a graphics API
+    if (cfg.enableBatchRenderer)
+        req(hs_enable_views(impl_->sim, (int)cfg.batchRenderViewWidth, (int)cfg.batchRenderViewHeight,
+                            cfg.renderDataDir), "hs_enable_views");
 }
 
 Manager::~Manager()
@@ -77,6 +82,7 @@ Manager::~Manager()
 void Manager::init()
 {
     req(hs_init(impl_->sim, nullptr), "hs_init");
+    if (impl_->cfg.enableBatchRenderer) req(hs_render_views(impl_->sim, nullptr), "hs_render_views");   // :878-880
     req(hs_sync(impl_->sim, nullptr), "hs_sync");
 }
 
@@ -86,10 +92,15 @@ void Manager::init()
 void Manager::step()
 {
     req(hs_step(impl_->sim, nullptr), "hs_step");
+    if (impl_->cfg.enableBatchRenderer) req(hs_render_views(impl_->sim, nullptr), "hs_render_views");   // :900-902
     req(hs_sync(impl_->sim, nullptr), "hs_sync");
 }
 
-void Manager::stepAsync(void *stream) { req(hs_step(impl_->sim, stream), "hs_step"); }
+void Manager::stepAsync(void *stream)
+{
+    req(hs_step(impl_->sim, stream), "hs_step");
+    if (impl_->cfg.enableBatchRenderer) req(hs_render_views(impl_->sim, stream), "hs_render_views");
+}
 void Manager::sync(void *stream) { req(hs_sync(impl_->sim, stream), "hs_sync"); }
 
 void Manager::stepHost(void *stream, const int32_t *actions, float *reward, int32_t *done)
@@ -105,9 +116,17 @@ void Manager::saveCheckpoint(madrona::CountT world_idx)
 void Manager::loadCheckpoint(madrona::CountT world_idx)
 {
     req(hs_load_checkpoint(impl_->sim, world_idx), "hs_load_checkpoint");
+    if (impl_->cfg.enableBatchRenderer) {       // src/mgr.cpp:960-962
+        req(hs_render_views(impl_->sim, nullptr), "hs_render_views");
+        req(hs_sync(impl_->sim, nullptr), "hs_sync");
+    }
 }
 
-void Manager::loadCheckpoints() { req(hs_load_checkpoints(impl_->sim, nullptr), "hs_load_checkpoints"); }
+void Manager::loadCheckpoints()
+{
+    req(hs_load_checkpoints(impl_->sim, nullptr), "hs_load_checkpoints");
+    if (impl_->cfg.enableBatchRenderer) req(hs_render_views(impl_->sim, nullptr), "hs_render_views");   // :982-984
+}
 
 static Tensor exported(const hs_sim *sim, int gpu, int id)
 {
@@ -147,8 +166,16 @@ HS_GETTER(episodeResultTensor, HS_EXPORT_EPISODE_RESULT)
 #undef HS_GETTER
 
 // src/mgr.cpp:1241-1263: renderer outputs
-Tensor Manager::depthTensor() const { fatal("depthTensor: batch renderer unavailable on this box"); }
-Tensor Manager::rgbTensor() const { fatal("rgbTensor: batch renderer unavailable on this box"); }
+Tensor Manager::depthTensor() const
+{
+    if (!impl_->cfg.enableBatchRenderer) fatal("depthTensor: enableBatchRenderer is false");
+    return exported(impl_->sim, impl_->cfg.gpuID, HS_EXPORT_VIEW_DEPTH);
+}
+Tensor Manager::rgbTensor() const
+{
+    if (!impl_->cfg.enableBatchRenderer) fatal("rgbTensor: enableBatchRenderer is false");
+    return exported(impl_->sim, impl_->cfg.gpuID, HS_EXPORT_VIEW_RGB);
+}
 madrona::render::RenderManager &Manager::getRenderManager()
 {
     fatal("getRenderManager: batch renderer unavailable on this box");

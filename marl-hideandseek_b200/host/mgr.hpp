@@ -6,8 +6,11 @@
 //
 // Differences, all forced by the environment (DESIGN.md "Boundary"):
 //   * execMode must be ExecMode::CUDA: there is no CPU backend and no fallback.
-//   * enableBatchRenderer must be false; depthTensor()/rgbTensor()/getRenderManager() abort
-//     (graphics APIs are unavailable on this box).
+//   * enableBatchRenderer = true turns on a CUDA ray caster for the per-agent views
+//     (depthTensor()/rgbTensor(), csrc/hs_views.cuh) instead of the Vulkan rasteriser;
+//     extRenderAPI/extRenderDev and getRenderManager() abort (graphics APIs are unavailable
+//     on this box).  Config::renderDataDir (extension): the reference's data/ directory with
+//     the render OBJ meshes; nullptr = $HIDESEEK_DATA_DIR, else built-in meshes.
 //   * Config::worldBase (extension, default 0): global index of this Manager's world 0, used
 //     to key the episode RNG when worlds are sharded across GPUs (one Manager per GPU).
 #pragma once
@@ -36,6 +39,7 @@ public:
         uint32_t batchRenderViewWidth = 64, batchRenderViewHeight = 64;
         madrona::render::APIBackend *extRenderAPI = nullptr;  madrona::render::GPUDevice *extRenderDev = nullptr;
         uint32_t worldBase = 0;      // extension: first global world index of this shard
+        const char *renderDataDir = nullptr;     // extension: render OBJ directory for the agent views
     };
 
 

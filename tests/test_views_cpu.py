@@ -1,0 +1,122 @@
+"""Agent-view ray caster, CPU side: the oracle restatement against closed-form scenes, and
+the product's render-mesh table (built-in shapes vs the reference's OBJ files where present)."""
+import math
+
+import numpy as np
+import pytest
+
+import views_util as vu
+
+pytestmark = pytest.mark.skipif(not vu.available(), reason="oracle/_ref/libviews_oracle.so not built")
+
+ID = [1.0, 0.0, 0.0, 0.0]
+OBJ_PLANE, OBJ_CUBE, OBJ_WALL, OBJ_HIDER, OBJ_SEEKER, OBJ_RAMP, OBJ_BOX = 1, 2, 3, 4, 5, 6, 7
+
+
+def table(data_dir=None):
+    import gpu_hideseek as gh
+    return gh.view_mesh_table(data_dir)
+
+
+def pixel_dirs(w=64, h=64, fov=100.0):
+    """Closed form of calculateOutRay for an identity camera: forward +y, right +x, rows go down."""
+    t = math.tan(math.radians(fov / 2))
+    px = (np.arange(w) + 0.5) / w
+    py = (np.arange(h) + 0.5) / h
+    x = (2 * px - 1) * t
+    z = -(2 * py - 1) * t
+    d = np.stack(np.broadcast_arrays(x[None, :], np.ones((h, w)), z[:, None]), -1)
+    return d / np.linalg.norm(d, axis=-1, keepdims=True)
+
+
+def test_ground_plane_closed_form():
+    m = vu.Meshes(table())
+    cam = [3.0, -2.0, 1.0]          # camera ends up at z = 1.5
+    depth, rgb = vu.render(m, [OBJ_PLANE], [[0, 0, 0]], [ID], [[1, 1, 1]], cam, ID)
+    d = pixel_dirs()
+    down = d[..., 2] < 0
+    want = np.where(down, 1.5 / np.maximum(-d[..., 2], 1e-9), 0.0)
+    assert np.allclose(depth[down], want[down], rtol=2e-4)   # grazing rows amplify fp32 rounding of d.z
+    assert (depth[~down] == 0).all() and (rgb[~down][:, :3] == 0).all()
+    assert (rgb[..., 3] == 255).all()
+    # floor material (0.5, 0.3, 0.3) * 0.2 * 255, truncated
+    assert (rgb[down][:, :3] == [25, 15, 15]).all()
+
+
+def test_cube_front_face_and_scale():
+    m = vu.Meshes(table())
+    # a cube scaled (1, 2, 1) centred 6 ahead: its front face is the plane y = 4
+    depth, rgb = vu.render(m, [OBJ_CUBE], [[0, 6, 0.5]], [ID], [[1, 2, 1]], [0, 0, 0], ID)
+    d = pixel_dirs()
+    t = 4.0 / d[..., 1]
+    hitp = d * t[..., None]
+    inside = (np.abs(hitp[..., 0]) < 0.999) & (np.abs(hitp[..., 2]) < 0.999)    # cam z = 0.5 = cube centre z
+    assert inside.sum() > 100
+    assert np.allclose(depth[inside], t[inside], rtol=2e-5)
+    assert (rgb[inside][:, :3] == [51, 5, 5]).all()
+    outside = (np.abs(hitp[..., 0]) > 1.001) | (np.abs(hitp[..., 2]) > 1.001)
+    assert (depth[outside] == 0).all()
+
+
+def test_backfaces_are_culled_and_rotation():
+    m = vu.Meshes(table())
+    # camera inside a wall block sees nothing of it; a seeker behind the camera is not seen
+    depth, _ = vu.render(m, [OBJ_WALL, OBJ_SEEKER], [[0, 0, -3], [0, -5, 0]], [ID, ID], [[3, 3, 3], [1, 1, 1]],
+                         [0, 0, -0.58], ID)
+    assert (depth == 0).all()
+    # turn the camera by 180 deg about z: the seeker (radius ~0.93 sphere) fills the centre
+    q = [0.0, 0.0, 0.0, 1.0]
+    depth, _ = vu.render(m, [OBJ_WALL, OBJ_SEEKER], [[0, 0, -3], [0, -5, 0]], [ID, ID], [[3, 3, 3], [1, 1, 1]],
+                         [0, 0, -0.58], q)
+    c = depth[30:34, 30:34]
+    assert (c > 3.9).all() and (c < 4.4).all()
+
+
+@pytest.mark.skipif(not vu.have_ref_data(), reason="reference render meshes not present")
+def test_builtin_meshes_match_reference_objs():
+    tb, tr = table(), table(vu.REF_DATA)
+    mb, mr = vu.Meshes(tb), vu.Meshes(tr)
+    # boxes, wedge and ground quad: identical surfaces -> identical images
+    rng = np.random.RandomState(0)
+    objs = [OBJ_PLANE, OBJ_CUBE, OBJ_WALL, OBJ_RAMP, OBJ_BOX, OBJ_WALL]
+    pos = np.array([[0, 0, 0], [2, 7, 1], [-4, 9, 0], [5, 5, 1], [-2, 14, 1], [0, 20, 0]], np.float32)
+    rot = rng.randn(6, 4).astype(np.float32)
+    rot[:, 1:3] = 0
+    rot /= np.linalg.norm(rot, axis=1, keepdims=True)
+    rot[0] = ID
+    scale = np.array([[1, 1, 1], [1, 1, 1], [2, 0.2, 1], [1, 1, 1], [1, 1, 1], [9, 0.2, 1]], np.float32)
+    db, cb = vu.render(mb, objs, pos, rot, scale, [0, 0, 1.0], ID)
+    dr, cr = vu.render(mr, objs, pos, rot, scale, [0, 0, 1.0], ID)
+    ok, frac, maxd = vu.compare(db, cb, dr, cr, tol=1e-5, max_flip_frac=1e-3)
+    assert ok, (frac, maxd)
+    assert (db > 0).mean() > 0.5
+    # object boxes agree (agents: the stand-in is within 1% of the mesh extents)
+    for o in (OBJ_CUBE, OBJ_WALL, OBJ_RAMP, OBJ_BOX):
+        assert np.array_equal(tb["obj_aabb"][o], tr["obj_aabb"][o]), o
+    assert np.abs(tb["obj_aabb"][OBJ_HIDER] - tr["obj_aabb"][OBJ_HIDER]).max() < 0.01
+    # the agent stand-in (geodesic ellipsoids) against the reference's 3 x 480-triangle mesh
+    db, cb = vu.render(mb, [OBJ_HIDER], [[0.3, 2, 0.2]], [rot[1]], [[1, 1, 1]], [0, 0, 0], ID)
+    dr, cr = vu.render(mr, [OBJ_HIDER], [[0.3, 2, 0.2]], [rot[1]], [[1, 1, 1]], [0, 0, 0], ID)
+    both = (db > 0) & (dr > 0)
+    assert both.sum() > 500
+    # faceting of two different tessellations of the same ellipsoids; the few larger
+    # differences are pixels on the eye / body outline
+    diff = np.abs(db - dr)[both]
+    assert np.median(diff) < 0.01 and np.percentile(diff, 99) < 0.1, (np.median(diff), np.percentile(diff, 99))
+    assert ((db > 0) != (dr > 0)).mean() < 0.01        # silhouettes differ by part of a pixel ring
+    assert tr["num_tris"] == 2 + 12 * 3 + 8 + 1440
+
+
+def test_table_capacity_and_clusters():
+    for d in ([None, vu.REF_DATA] if vu.have_ref_data() else [None]):
+        t = table(d)
+        assert t["num_tris"] <= 1600 and t["num_clusters"] <= 160 and t["num_sub"] <= 16
+        # every triangle lies inside its cluster box, every cluster inside its submesh box
+        for s in range(int(t["num_sub"])):
+            sb = t["sub"][s]
+            for c in range(int(sb["count"])):
+                cb = t["cluster"][int(sb["first"]) + c]
+                assert 0 < cb["count"] <= 16
+                tri = t["tri"][int(cb["first"]):int(cb["first"]) + int(cb["count"])].reshape(-1, 3)
+                assert (tri >= cb["lo"]).all() and (tri <= cb["hi"]).all()
+                assert (cb["lo"] >= sb["lo"] - 1e-4).all() and (cb["hi"] <= sb["hi"] + 1e-4).all()
