@@ -86,8 +86,18 @@ def test_no_cpu_backend():
     import gpu_hideseek as gh
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         gh.HideAndSeekSimulator(exec_mode=gh.madrona.ExecMode.CPU, num_worlds=2)
-    with pytest.raises(RuntimeError, match="renderer"):
-        gh.HideAndSeekSimulator(num_worlds=2, enable_batch_renderer=True)
+
+
+def test_view_entry_points_reject_bad_arguments():
+    # host-side argument checks of the agent-view entry points (no device needed)
+    import gpu_hideseek as gh
+    lib = gh.load_library()
+    assert lib.hs_enable_views(None, 64, 64, None) != 0
+    assert lib.hs_render_views(None, None) != 0
+    with pytest.raises(RuntimeError, match="cannot open"):
+        gh.view_mesh_table("/nonexistent-data-dir")
+    t = gh.view_mesh_table()
+    assert t["num_tris"] > 0 and abs(float(t["fov_scale"]) - 0.8390996) < 1e-6
 
 
 @pytest.mark.skipif(_has_gpu(), reason="checks the no-GPU failure path")
