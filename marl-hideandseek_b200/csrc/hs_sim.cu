@@ -25,10 +25,12 @@
 #include "hs_narrowphase.cuh"
 #include "hs_solver.cuh"
 #include "hs_checkpoint.cuh"
+#define HS_VIEWS_HOST_ONLY
 #include "hs_views.cuh"
 
 namespace hs {
 void buildAssetTable(AssetTable &T);
+cudaError_t launchAgentViews(const DeviceState &S, const ViewParams &P, unsigned views, cudaStream_t stream);   // hs_views.cu
 }
 
 using namespace hs;
@@ -507,8 +509,7 @@ extern "C" int hs_render_views(hs_sim *sim, void *stream)
     if (!sim->viewsEnabled) { g_err = "hs_render_views: agent views are not enabled (hs_enable_views)"; return 1; }
     HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
     const unsigned views = unsigned(sim->cfg.num_worlds) * sim->S.p.agentsPerWorld;
-    k_agent_views<<<views, kViewThreads, 0, (cudaStream_t)stream>>>(sim->S, sim->view);
-    HS_CUDA(cudaGetLastError());
+    HS_CUDA(launchAgentViews(sim->S, sim->view, views, (cudaStream_t)stream));
     return 0;
 }
 

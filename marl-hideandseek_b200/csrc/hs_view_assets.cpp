@@ -235,7 +235,15 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
 
     int meshFirstSub[M_COUNT], meshNumSub[M_COUNT];
     float meshAabb[M_COUNT][6];
-    for (int i = 0; i < M_COUNT; i++) {
+    // single-cluster meshes first: their triangles are what the kernel stages in shared memory
+    auto isSmall = [&](int i) { return src[i].subs.size() == 1 && (int)src[i].subs[0].tris.size() <= kViewClusterTris; };
+    std::vector<int> order;
+    for (int i = 0; i < M_COUNT; i++) if (isSmall(i)) order.push_back(i);
+    const size_t numSmallMeshes = order.size();
+    for (int i = 0; i < M_COUNT; i++) if (!isSmall(i)) order.push_back(i);
+    for (size_t oi = 0; oi < order.size(); oi++) {
+        const int i = order[oi];
+        if (oi == numSmallMeshes) T.numSmallTris = T.numTris <= kViewSmallTris ? T.numTris : 0;
         MeshSrc &m = src[i];
         if ((int)m.subs.size() > kViewMaxSubPerObj || T.numSub + (int)m.subs.size() > kViewMaxSubmeshes) {
             g_viewErr = "render mesh has too many submeshes";
@@ -247,6 +255,7 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
         for (SubSrc &s : m.subs) {
             std::vector<std::pair<int, int>> cl;
             splitClusters(s.tris, 0, (int)s.tris.size(), cl);
+            if (cl.size() > 32) { g_viewErr = "render submesh needs more than 32 clusters"; return g_viewErr.c_str(); }
             if (T.numClusters + (int)cl.size() > kViewMaxClusters || T.numTris + (int)s.tris.size() > kViewMaxTris) {
                 g_viewErr = "render meshes exceed the view table capacity";
                 return g_viewErr.c_str();
@@ -268,6 +277,7 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
             for (const Tri &t : s.tris) std::memcpy(T.tri[T.numTris++], t.v, sizeof(t.v));
         }
     }
+    if (numSmallMeshes == order.size()) T.numSmallTris = T.numTris <= kViewSmallTris ? T.numTris : 0;
     // the cluster / submesh boxes cull in object space: pad them like the instance boxes
     auto pad = [](ViewBox &b) {
         for (int k = 0; k < 3; k++) {

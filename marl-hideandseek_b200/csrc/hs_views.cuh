@@ -14,8 +14,11 @@
 //     creates no light entities, so computeFragment's colour is max(0.2, 0) * material colour
 //     (bvh_raycast.cpp:848-935); rgb bytes = colour * 255 truncated, alpha 255 (:822-839).
 // What differs by design: no TLAS/BLAS walk — a world has <= 52 instances, so a CTA stages
-// their object-space transforms and world AABBs in shared memory once per view and every
-// pixel runs one uniform loop over them (slab cull, then the mesh's triangle clusters).
+// their object-space transforms and world AABBs in shared memory once per view, sorted front
+// to back, and every pixel runs one uniform loop over them (slab cull against the closest hit
+// so far, then the mesh's triangles).  Which triangles of a box / wedge / ground instance face
+// the camera is decided once per view, not per pixel.  This file is its own translation unit
+// (hs_views.cu) compiled with FMA contraction on: nothing here has to match a CPU bit for bit.
 // Texture lookups (plane grid, agent faces) are not reproduced: textured materials use their
 // base colour.  Inactive agent slots produce an all-zero view.
 #pragma once
@@ -30,6 +33,7 @@ constexpr int kViewMaxSubmeshes = 16;
 constexpr int kViewMaxSubPerObj = 3;
 constexpr int kViewClusterTris = 16;
 constexpr int kViewThreads = 256;
+constexpr int kViewSmallTris = 64;     // triangles of the single-cluster meshes, staged in shared memory
 
 struct ViewBox { float lo[3]; int first; float hi[3]; int count; };     // 32 B
 struct ViewMeshTable {
@@ -38,7 +42,8 @@ struct ViewMeshTable {
     float subColor[OBJ_COUNT][kViewMaxSubPerObj][3];   // material base colour of (object, submesh)
     ViewBox sub[kViewMaxSubmeshes];                    // first/count index clusters
     ViewBox cluster[kViewMaxClusters];                 // first/count index triangles
-    int numSub, numClusters, numTris, pad;
+    int numSub, numClusters, numTris;
+    int numSmallTris;                                  // tri[0, numSmallTris): single-cluster meshes, stored first
     float fovScale;                                    // 1 / tanf(toRadians(100 / 2))
     float tri[kViewMaxTris][9];                        // a, b, c in object space
 };
@@ -53,15 +58,23 @@ struct ViewParams {
 #if defined(__CUDACC__) && !defined(HS_VIEWS_HOST_ONLY)
 
 struct ViewInst {
-    Vec3 lo, hi;             // world AABB of the instance's render mesh
+    Vec3 lo, hi;             // world AABB of the instance's render mesh (padded)
     Vec3 ro;                 // camera origin in object space
     Quat qinv;
     Vec3 invS;
-    int obj;
+    int obj;                 // -1: nothing to hit (no mesh, zero scale, or no front-facing triangle)
+    // single-cluster meshes (ground, boxes, wedge): triangle range in the shared-memory copy and
+    // the subset that faces the camera; mask == 0 with triCount == 0 marks a clustered mesh
+    int triFirst, triCount;
+    uint32_t mask;
+    // clustered meshes (agents): per submesh, the clusters holding a triangle that faces the camera
+    uint32_t cmask[kViewMaxSubPerObj];
 };
 
 struct ViewSmem {
-    ViewInst inst[kMaxBodies];
+    ViewInst inst[kMaxBodies];           // front to back by distance from the camera to the box
+    float key[kMaxBodies];
+    float tri[kViewSmallTris][9];
     int numInst;
     int active;
     Vec3 origin, lowerLeft, horizontal, vertical;
@@ -122,8 +135,20 @@ __device__ __forceinline__ bool viewSlab(const float *lo, const float *hi, Vec3 
     return aabbRayIntersects({lo[0], lo[1], lo[2]}, {hi[0], hi[1], hi[2]}, o, inv_d, 0.f, t_max);
 }
 
+// A triangle can only be hit from its front side (back-face culling), and which side the camera
+// is on does not depend on the pixel: decide it once per (view, instance).  The test keeps a
+// triangle whenever the camera is not clearly behind it, so it never drops one the per-ray
+// test would have accepted.
+__device__ __forceinline__ bool viewFacesCamera(const float *t9, Vec3 ro)
+{
+    Vec3 a = {t9[0], t9[1], t9[2]};
+    Vec3 n = cross(v3(t9[3], t9[4], t9[5]) - a, v3(t9[6], t9[7], t9[8]) - a);
+    Vec3 r = ro - a;
+    return dot(n, r) >= -1e-4f * length(n) * fmaxf(1.f, length(r));
+}
+
 // One CTA per view (world, agent slot); a warp shades 8x4 pixel tiles.
-__global__ void __launch_bounds__(kViewThreads) k_agent_views(DeviceState S, ViewParams P)
+__global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, ViewParams P)
 {
     __shared__ ViewSmem sm;
     const int A = S.p.agentsPerWorld;
@@ -152,6 +177,7 @@ __global__ void __launch_bounds__(kViewThreads) k_agent_views(DeviceState S, Vie
             sm.lowerLeft = start - sm.horizontal / 2.f - sm.vertical / 2.f + forward;
         }
     }
+    for (int i = tid; i < M.numSmallTris * 9; i += kViewThreads) (&sm.tri[0][0])[i] = (&M.tri[0][0])[i];
     __syncthreads();
     const size_t pixBase = size_t(view) * W * H;
     if (!sm.active) {
@@ -162,16 +188,17 @@ __global__ void __launch_bounds__(kViewThreads) k_agent_views(DeviceState S, Vie
         return;
     }
     const int nInst = sm.numInst;
+    ViewInst I;
+    float key = 0.f;
     if (tid < nInst) {
-        ViewInst I;
         uint32_t m = META(S, tid, w);
         I.obj = metaObj(m);
         Pose ps = loadPose(S, REC_POSE, tid, w);
         Vec3 sc = loadScale(S, tid, w);
         // instanceHasVolume (bvh_raycast.cpp:272-277) and meshes this table does not carry
         bool skip = (sc.x == 0.f && sc.y == 0.f && sc.z == 0.f) || M.objNumSub[I.obj] == 0;
-        if (skip) I.obj = -1;
-        const float *bb = M.objAabb[I.obj < 0 ? 0 : I.obj];
+        const int obj = skip ? 0 : I.obj;
+        const float *bb = M.objAabb[obj];
         AABB wb = aabbApplyTRS({{bb[0], bb[1], bb[2]}, {bb[3], bb[4], bb[5]}}, ps.x, ps.q, sc);
         // the cull must never reject a ray the triangle test would accept: pad by rounding slack
         Vec3 ext = (wb.hi - wb.lo) * 1e-5f + v3(1e-5f, 1e-5f, 1e-5f);
@@ -179,7 +206,52 @@ __global__ void __launch_bounds__(kViewThreads) k_agent_views(DeviceState S, Vie
         I.qinv = qinv(ps.q);
         I.invS = {1.f / sc.x, 1.f / sc.y, 1.f / sc.z};
         I.ro = mulDiag(I.invS, rotate(I.qinv, sm.origin - ps.x));
-        sm.inst[tid] = I;
+        I.triFirst = 0; I.triCount = 0; I.mask = 0;
+        for (int s = 0; s < kViewMaxSubPerObj; s++) I.cmask[s] = 0;
+        if (!skip && M.objNumSub[obj] == 1) {
+            const ViewBox &SB = M.sub[M.objFirstSub[obj]];
+            const ViewBox &CB = M.cluster[SB.first];
+            if (SB.count == 1 && CB.first + CB.count <= M.numSmallTris) {
+                I.triFirst = CB.first; I.triCount = CB.count;
+                for (int t = 0; t < CB.count; t++)
+                    if (viewFacesCamera(sm.tri[CB.first + t], I.ro)) I.mask |= 1u << t;
+                if (I.mask == 0) skip = true;
+            }
+        }
+        if (skip) I.obj = -1;
+        // distance from the camera to the box (0 inside): the visiting order
+        Vec3 o = sm.origin;
+        Vec3 dl = vmax(vmax(I.lo - o, o - I.hi), v3(0.f, 0.f, 0.f));
+        key = skip ? 3.0e38f : length2(dl);
+        sm.key[tid] = key;
+    }
+    __syncthreads();
+    if (tid < nInst) {
+        int rank = 0;
+        for (int j = 0; j < nInst; j++) {
+            float kj = sm.key[j];
+            rank += (kj < key || (kj == key && j < tid)) ? 1 : 0;
+        }
+        sm.inst[rank] = I;
+    }
+    __syncthreads();
+    // clustered instances: thread per cluster marks the clusters with a camera-facing triangle
+    // (a camera inside a closed mesh — every agent sits inside its own body — faces none of it)
+    for (int i = 0; i < nInst; i++) {
+        ViewInst &J = sm.inst[i];
+        if (J.obj < 0) break;
+        if (J.triCount > 0) continue;
+        const int s0 = M.objFirstSub[J.obj], ns = M.objNumSub[J.obj];
+        const Vec3 ro = J.ro;
+        for (int s = 0; s < ns; s++) {
+            const ViewBox &SB = M.sub[s0 + s];
+            for (int c = tid; c < SB.count; c += kViewThreads) {
+                const ViewBox &CB = M.cluster[SB.first + c];
+                bool any = false;
+                for (int t = 0; t < CB.count; t++) any |= viewFacesCamera(M.tri[CB.first + t], ro);
+                if (any) atomicOr(&J.cmask[s], 1u << c);
+            }
+        }
     }
     __syncthreads();
 
@@ -197,31 +269,40 @@ __global__ void __launch_bounds__(kViewThreads) k_agent_views(DeviceState S, Vie
         float best = 10000.f;
         int hitObj = -1, hitSub = 0;
         for (int i = 0; i < nInst; i++) {
-            const ViewInst &I = sm.inst[i];
-            if (I.obj < 0) continue;
-            if (!aabbRayIntersects(I.lo, I.hi, o, invd, 0.f, best)) continue;
-            Vec3 rd = mulDiag(I.invS, rotate(I.qinv, d));
+            const ViewInst &J = sm.inst[i];
+            if (J.obj < 0) break;                                 // skipped instances sort last
+            if (!aabbRayIntersects(J.lo, J.hi, o, invd, 0.f, best)) continue;
+            Vec3 rd = mulDiag(J.invS, rotate(J.qinv, d));
             float ts = length(rd);
             rd = rd / ts;
-            Vec3 ro = I.ro;
+            const Vec3 ro = J.ro;
             float tmax = best * ts;
             WoopRay R = woopSetup(rd);
-            Vec3 invrd = {1.f / rd.x, 1.f / rd.y, 1.f / rd.z};
             bool hit = false;
-            const int s0 = M.objFirstSub[I.obj], ns = M.objNumSub[I.obj];
-            for (int s = 0; s < ns; s++) {
-                const ViewBox &SB = M.sub[s0 + s];
-                if (ns > 1 && !viewSlab(SB.lo, SB.hi, ro, invrd, tmax)) continue;
-                for (int c = 0; c < SB.count; c++) {
-                    const ViewBox &CB = M.cluster[SB.first + c];
-                    if (SB.count > 1 && !viewSlab(CB.lo, CB.hi, ro, invrd, tmax)) continue;
-                    for (int t = 0; t < CB.count; t++) {
-                        float th = woopHit(M.tri[CB.first + t], R, ro, tmax);
-                        if (th >= 0.f) { tmax = th; hit = true; hitSub = s; }
+            if (J.triCount > 0) {
+                for (uint32_t m = J.mask; m; m &= m - 1) {
+                    float th = woopHit(sm.tri[J.triFirst + __ffs(m) - 1], R, ro, tmax);
+                    if (th >= 0.f) { tmax = th; hit = true; hitSub = 0; }
+                }
+            } else {
+                Vec3 invrd = {1.f / rd.x, 1.f / rd.y, 1.f / rd.z};
+                const int s0 = M.objFirstSub[J.obj], ns = M.objNumSub[J.obj];
+                for (int s = 0; s < ns; s++) {
+                    uint32_t cm = J.cmask[s];
+                    if (cm == 0) continue;
+                    const ViewBox &SB = M.sub[s0 + s];
+                    if (ns > 1 && !viewSlab(SB.lo, SB.hi, ro, invrd, tmax)) continue;
+                    for (; cm; cm &= cm - 1) {
+                        const ViewBox &CB = M.cluster[SB.first + __ffs(cm) - 1];
+                        if (!viewSlab(CB.lo, CB.hi, ro, invrd, tmax)) continue;
+                        for (int t = 0; t < CB.count; t++) {
+                            float th = woopHit(M.tri[CB.first + t], R, ro, tmax);
+                            if (th >= 0.f) { tmax = th; hit = true; hitSub = s; }
+                        }
                     }
                 }
             }
-            if (hit) { best = tmax / ts; hitObj = I.obj; }
+            if (hit) { best = tmax / ts; hitObj = J.obj; }
         }
         const size_t pix = pixBase + size_t(py) * W + px;
         uint32_t rgba = 0xFF000000u;
