@@ -58,15 +58,14 @@ struct ViewParams {
 #if defined(__CUDACC__) && !defined(HS_VIEWS_HOST_ONLY)
 
 struct ViewInst {
-    Vec3 lo, hi;             // world AABB of the instance's render mesh (padded)
+    Vec3 lo; int obj;        // world AABB of the instance's render mesh (padded); obj -1: nothing to
+    Vec3 hi; uint32_t mask;  //   hit (no mesh, zero scale, or no camera-facing triangle)
     Vec3 ro;                 // camera origin in object space
-    Quat qinv;
-    Vec3 invS;
-    int obj;                 // -1: nothing to hit (no mesh, zero scale, or no front-facing triangle)
-    // single-cluster meshes (ground, boxes, wedge): triangle range in the shared-memory copy and
-    // the subset that faces the camera; mask == 0 with triCount == 0 marks a clustered mesh
+    // world -> object direction map scale^-1 * R^T, by columns (images of the world axes)
+    Vec3 cx, cy, cz;
+    // single-cluster meshes (ground, boxes, wedge): triangle range in the shared-memory copy;
+    // `mask` = the subset that faces the camera.  triCount == 0 marks a clustered mesh.
     int triFirst, triCount;
-    uint32_t mask;
     // clustered meshes (agents): per submesh, the clusters holding a triangle that faces the camera
     uint32_t cmask[kViewMaxSubPerObj];
 };
@@ -75,15 +74,16 @@ struct ViewSmem {
     ViewInst inst[kMaxBodies];           // front to back by distance from the camera to the box
     float key[kMaxBodies];
     float tri[kViewSmallTris][9];
-    int numInst;
+    int numInst;                         // instances worth visiting (skipped ones sort last)
     int active;
     Vec3 origin, lowerLeft, horizontal, vertical;
 };
 
-struct WoopRay { int kx, ky, kz; float Sx, Sy, Sz; };
+// Woop et al. ray constants: permutation (kz = dominant axis), shear, and the ray origin permuted
+struct WoopRay { int kx, ky, kz; float Sx, Sy, Sz; float ox, oy, oz; };
 
 // computeRayIsectInfo (bvh_raycast.cpp:228-270)
-__device__ __forceinline__ WoopRay woopSetup(Vec3 d)
+__device__ __forceinline__ WoopRay woopSetup(Vec3 d, Vec3 org)
 {
     float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
     int kz = (ax > ay && ax > az) ? 0 : (ay > az ? 1 : 2);
@@ -92,19 +92,18 @@ __device__ __forceinline__ WoopRay woopSetup(Vec3 d)
     float dz = comp(d, kz);
     if (dz < 0.f) { int t = kx; kx = ky; ky = t; }
     float inv = 1.f / dz;
-    return {kx, ky, kz, comp(d, kx) * inv, comp(d, ky) * inv, inv};
+    return {kx, ky, kz, comp(d, kx) * inv, comp(d, ky) * inv, inv, comp(org, kx), comp(org, ky), comp(org, kz)};
 }
 
 // rayTriangleIntersection with back-face culling (bvh_raycast.cpp:317-447); returns the hit
-// distance in object-space units of the normalised ray, or a negative value on a miss.
-__device__ __forceinline__ float woopHit(const float *t9, const WoopRay &R, Vec3 org, float t_max)
+// distance in object-space units of the normalised ray, or a negative value on a miss.  The
+// axis permutation is applied by indexing the triangle's nine floats, not by selecting
+// between loaded components.
+__device__ __forceinline__ float woopHit(const float *t9, const WoopRay &R, float t_max)
 {
-    Vec3 A = {t9[0] - org.x, t9[1] - org.y, t9[2] - org.z};
-    Vec3 B = {t9[3] - org.x, t9[4] - org.y, t9[5] - org.z};
-    Vec3 C = {t9[6] - org.x, t9[7] - org.y, t9[8] - org.z};
-    float a_kz = comp(A, R.kz), a_kx = comp(A, R.kx), a_ky = comp(A, R.ky);
-    float b_kz = comp(B, R.kz), b_kx = comp(B, R.kx), b_ky = comp(B, R.ky);
-    float c_kz = comp(C, R.kz), c_kx = comp(C, R.kx), c_ky = comp(C, R.ky);
+    const float a_kx = t9[R.kx] - R.ox, a_ky = t9[R.ky] - R.oy, a_kz = t9[R.kz] - R.oz;
+    const float b_kx = t9[3 + R.kx] - R.ox, b_ky = t9[3 + R.ky] - R.oy, b_kz = t9[3 + R.kz] - R.oz;
+    const float c_kx = t9[6 + R.kx] - R.ox, c_ky = t9[6 + R.ky] - R.oy, c_kz = t9[6 + R.kz] - R.oz;
     float Ax = fmaf(-R.Sx, a_kz, a_kx), Ay = fmaf(-R.Sy, a_kz, a_ky);
     float Bx = fmaf(-R.Sx, b_kz, b_kx), By = fmaf(-R.Sy, b_kz, b_ky);
     float Cx = fmaf(-R.Sx, c_kz, c_kx), Cy = fmaf(-R.Sy, c_kz, c_ky);
@@ -112,10 +111,10 @@ __device__ __forceinline__ float woopHit(const float *t9, const WoopRay &R, Vec3
     float V = fmaf(Ax, Cy, -Ay * Cx);
     float W = fmaf(Bx, Ay, -By * Ax);
     const float eps = 1e-7f;
-    if (U > -eps && U < eps) U = 0.f;
-    if (V > -eps && V < eps) V = 0.f;
-    if (W > -eps && W < eps) W = 0.f;
-    if (U < 0.f || V < 0.f || W < 0.f) return -1.f;
+    if (fabsf(U) < eps) U = 0.f;
+    if (fabsf(V) < eps) V = 0.f;
+    if (fabsf(W) < eps) W = 0.f;
+    if (fminf(U, fminf(V, W)) < 0.f) return -1.f;
     if (U == 0.f || V == 0.f || W == 0.f) {
         U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
         V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
@@ -147,6 +146,13 @@ __device__ __forceinline__ bool viewFacesCamera(const float *t9, Vec3 ro)
     return dot(n, r) >= -1e-4f * length(n) * fmaxf(1.f, length(r));
 }
 
+// Is the box [lo,hi] (relative to the apex) entirely outside the half space n.x >= 0 ?
+__device__ __forceinline__ bool viewBoxBehind(Vec3 n, Vec3 lo, Vec3 hi)
+{
+    float m = fmaxf(n.x * lo.x, n.x * hi.x) + fmaxf(n.y * lo.y, n.y * hi.y) + fmaxf(n.z * lo.z, n.z * hi.z);
+    return m < 0.f;
+}
+
 // One CTA per view (world, agent slot); a warp shades 8x4 pixel tiles.
 __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, ViewParams P)
 {
@@ -161,7 +167,6 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
     if (tid == 0) {
         int slot = WB(S, WB_IFACE_SLOT + k, w);
         sm.active = slot != 0xFF;
-        sm.numInst = WI(S, WF_NUM_BODIES, w);
         if (sm.active) {
             // viewTransformUpdate + calculateOutRay
             Pose ps = loadPose(S, REC_POSE, slot, w);
@@ -187,25 +192,30 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
         }
         return;
     }
-    const int nInst = sm.numInst;
+    const int nBodies = WI(S, WF_NUM_BODIES, w);
     ViewInst I;
     float key = 0.f;
-    if (tid < nInst) {
+    bool skip = true;
+    if (tid < nBodies) {
         uint32_t m = META(S, tid, w);
         I.obj = metaObj(m);
         Pose ps = loadPose(S, REC_POSE, tid, w);
         Vec3 sc = loadScale(S, tid, w);
         // instanceHasVolume (bvh_raycast.cpp:272-277) and meshes this table does not carry
-        bool skip = (sc.x == 0.f && sc.y == 0.f && sc.z == 0.f) || M.objNumSub[I.obj] == 0;
+        skip = (sc.x == 0.f && sc.y == 0.f && sc.z == 0.f) || M.objNumSub[I.obj] == 0;
         const int obj = skip ? 0 : I.obj;
         const float *bb = M.objAabb[obj];
         AABB wb = aabbApplyTRS({{bb[0], bb[1], bb[2]}, {bb[3], bb[4], bb[5]}}, ps.x, ps.q, sc);
         // the cull must never reject a ray the triangle test would accept: pad by rounding slack
         Vec3 ext = (wb.hi - wb.lo) * 1e-5f + v3(1e-5f, 1e-5f, 1e-5f);
         I.lo = wb.lo - ext; I.hi = wb.hi + ext;
-        I.qinv = qinv(ps.q);
-        I.invS = {1.f / sc.x, 1.f / sc.y, 1.f / sc.z};
-        I.ro = mulDiag(I.invS, rotate(I.qinv, sm.origin - ps.x));
+        // ray into object space (bvh_raycast.cpp:625-633): scale^-1 * rotateVec(rot^-1, .)
+        const Quat qi = qinv(ps.q);
+        const Vec3 invS = {1.f / sc.x, 1.f / sc.y, 1.f / sc.z};
+        I.ro = mulDiag(invS, rotate(qi, sm.origin - ps.x));
+        I.cx = mulDiag(invS, rotate(qi, v3(1.f, 0.f, 0.f)));
+        I.cy = mulDiag(invS, rotate(qi, v3(0.f, 1.f, 0.f)));
+        I.cz = mulDiag(invS, rotate(qi, v3(0.f, 0.f, 1.f)));
         I.triFirst = 0; I.triCount = 0; I.mask = 0;
         for (int s = 0; s < kViewMaxSubPerObj; s++) I.cmask[s] = 0;
         if (!skip && M.objNumSub[obj] == 1) {
@@ -225,31 +235,32 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
         key = skip ? 3.0e38f : length2(dl);
         sm.key[tid] = key;
     }
-    __syncthreads();
-    if (tid < nInst) {
+    const int live = __syncthreads_count(!skip);
+    if (tid < nBodies) {
         int rank = 0;
-        for (int j = 0; j < nInst; j++) {
+        for (int j = 0; j < nBodies; j++) {
             float kj = sm.key[j];
             rank += (kj < key || (kj == key && j < tid)) ? 1 : 0;
         }
         sm.inst[rank] = I;
     }
+    if (tid == 0) sm.numInst = live;
     __syncthreads();
+    const int nInst = live;
     // clustered instances: thread per cluster marks the clusters with a camera-facing triangle
     // (a camera inside a closed mesh — every agent sits inside its own body — faces none of it)
     for (int i = 0; i < nInst; i++) {
-        ViewInst &J = sm.inst[i];
-        if (J.obj < 0) break;
-        if (J.triCount > 0) continue;
-        const int s0 = M.objFirstSub[J.obj], ns = M.objNumSub[J.obj];
-        const Vec3 ro = J.ro;
+        if (sm.inst[i].triCount > 0) continue;
+        const int obj = sm.inst[i].obj;
+        const int s0 = M.objFirstSub[obj], ns = M.objNumSub[obj];
+        const Vec3 ro = sm.inst[i].ro;
         for (int s = 0; s < ns; s++) {
             const ViewBox &SB = M.sub[s0 + s];
             for (int c = tid; c < SB.count; c += kViewThreads) {
                 const ViewBox &CB = M.cluster[SB.first + c];
                 bool any = false;
                 for (int t = 0; t < CB.count; t++) any |= viewFacesCamera(M.tri[CB.first + t], ro);
-                if (any) atomicOr(&J.cmask[s], 1u << c);
+                if (any) atomicOr(&sm.inst[i].cmask[s], 1u << c);
             }
         }
     }
@@ -258,9 +269,41 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
     const int warp = tid >> 5, lane = tid & 31;
     const int tilesX = (W + 7) / 8, tilesY = (H + 3) / 4;
     const Vec3 o = sm.origin;
+    const Vec3 LL = sm.lowerLeft - o, HZ = sm.horizontal, VT = sm.vertical;
     for (int tile = warp; tile < tilesX * tilesY; tile += kViewThreads / 32) {
-        const int px = (tile % tilesX) * 8 + (lane & 7);
-        const int py = (tile / tilesX) * 4 + (lane >> 3);
+        const int px0 = (tile % tilesX) * 8, py0 = (tile / tilesX) * 4;
+        // Warp-cooperative cull: lane j tests instances j and j+32 against the pyramid of this
+        // 8x4-pixel tile (apex = camera, four side planes through the tile's corner rays); the
+        // rays then only visit the instances some ray of the tile can reach, still front to back.
+        uint64_t todo;
+        {
+            const float u0 = float(px0) / float(W), u1 = float(min(px0 + 8, W)) / float(W);
+            const float v0 = float(py0) / float(H), v1 = float(min(py0 + 4, H)) / float(H);
+            const Vec3 c00 = LL + u0 * HZ + v0 * VT, c10 = LL + u1 * HZ + v0 * VT;
+            const Vec3 c01 = LL + u0 * HZ + v1 * VT, c11 = LL + u1 * HZ + v1 * VT;
+            const Vec3 cen = c00 + c11;
+            Vec3 nl = cross(c00, c01), nr = cross(c10, c11), nt = cross(c00, c10), nb = cross(c01, c11);
+            if (dot(nl, cen) < 0.f) nl = -nl;
+            if (dot(nr, cen) < 0.f) nr = -nr;
+            if (dot(nt, cen) < 0.f) nt = -nt;
+            if (dot(nb, cen) < 0.f) nb = -nb;
+            bool keep[2];
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                const int j = lane + 32 * r;
+                keep[r] = false;
+                if (j < nInst) {
+                    // widen the box a little: the planes come out of rounded corner directions
+                    const Vec3 lo = sm.inst[j].lo - o, hi = sm.inst[j].hi - o;
+                    const Vec3 e = (hi - lo) * 1e-4f + v3(1e-4f, 1e-4f, 1e-4f);
+                    const Vec3 l2 = lo - e, h2 = hi + e;
+                    keep[r] = !(viewBoxBehind(nl, l2, h2) || viewBoxBehind(nr, l2, h2) ||
+                                viewBoxBehind(nt, l2, h2) || viewBoxBehind(nb, l2, h2));
+                }
+            }
+            todo = uint64_t(__ballot_sync(0xffffffffu, keep[0])) | (uint64_t(__ballot_sync(0xffffffffu, keep[1])) << 32);
+        }
+        const int px = px0 + (lane & 7), py = py0 + (lane >> 3);
         if (px >= W || py >= H) continue;
         float pu = (float(px) + 0.5f) / float(W);
         float pv = (float(py) + 0.5f) / float(H);
@@ -268,27 +311,29 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
         Vec3 invd = {1.f / d.x, 1.f / d.y, 1.f / d.z};
         float best = 10000.f;
         int hitObj = -1, hitSub = 0;
-        for (int i = 0; i < nInst; i++) {
-            const ViewInst &J = sm.inst[i];
-            if (J.obj < 0) break;                                 // skipped instances sort last
-            if (!aabbRayIntersects(J.lo, J.hi, o, invd, 0.f, best)) continue;
-            Vec3 rd = mulDiag(J.invS, rotate(J.qinv, d));
+        for (; todo; todo &= todo - 1) {
+            const int i = __ffsll((long long)todo) - 1;
+            if (!aabbRayIntersects(sm.inst[i].lo, sm.inst[i].hi, o, invd, 0.f, best)) continue;
+            Vec3 rd = d.x * sm.inst[i].cx + d.y * sm.inst[i].cy + d.z * sm.inst[i].cz;
             float ts = length(rd);
             rd = rd / ts;
-            const Vec3 ro = J.ro;
+            const Vec3 ro = sm.inst[i].ro;
             float tmax = best * ts;
-            WoopRay R = woopSetup(rd);
+            const WoopRay R = woopSetup(rd, ro);
             bool hit = false;
-            if (J.triCount > 0) {
-                for (uint32_t m = J.mask; m; m &= m - 1) {
-                    float th = woopHit(sm.tri[J.triFirst + __ffs(m) - 1], R, ro, tmax);
+            const int triCount = sm.inst[i].triCount;
+            if (triCount > 0) {
+                const int first = sm.inst[i].triFirst;
+                for (uint32_t m = sm.inst[i].mask; m; m &= m - 1) {
+                    float th = woopHit(sm.tri[first + __ffs(m) - 1], R, tmax);
                     if (th >= 0.f) { tmax = th; hit = true; hitSub = 0; }
                 }
             } else {
                 Vec3 invrd = {1.f / rd.x, 1.f / rd.y, 1.f / rd.z};
-                const int s0 = M.objFirstSub[J.obj], ns = M.objNumSub[J.obj];
+                const int obj = sm.inst[i].obj;
+                const int s0 = M.objFirstSub[obj], ns = M.objNumSub[obj];
                 for (int s = 0; s < ns; s++) {
-                    uint32_t cm = J.cmask[s];
+                    uint32_t cm = sm.inst[i].cmask[s];
                     if (cm == 0) continue;
                     const ViewBox &SB = M.sub[s0 + s];
                     if (ns > 1 && !viewSlab(SB.lo, SB.hi, ro, invrd, tmax)) continue;
@@ -296,13 +341,13 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
                         const ViewBox &CB = M.cluster[SB.first + __ffs(cm) - 1];
                         if (!viewSlab(CB.lo, CB.hi, ro, invrd, tmax)) continue;
                         for (int t = 0; t < CB.count; t++) {
-                            float th = woopHit(M.tri[CB.first + t], R, ro, tmax);
+                            float th = woopHit(M.tri[CB.first + t], R, tmax);
                             if (th >= 0.f) { tmax = th; hit = true; hitSub = s; }
                         }
                     }
                 }
             }
-            if (hit) { best = tmax / ts; hitObj = J.obj; }
+            if (hit) { best = tmax / ts; hitObj = sm.inst[i].obj; }
         }
         const size_t pix = pixBase + size_t(py) * W + px;
         uint32_t rgba = 0xFF000000u;
