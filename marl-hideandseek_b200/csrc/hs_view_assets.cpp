@@ -3,7 +3,7 @@
 // Replaces, for this environment's fixed asset set, loadRenderObjects (src/mgr.cpp:590-672):
 // the six render meshes, their per-submesh material colours, and — instead of Madrona's
 // per-mesh QBVH (M/include/madrona/mesh_bvh.hpp) — a two-level box hierarchy
-// (submesh -> clusters of <= 16 triangles) sized for meshes of 2..1440 triangles.
+// (submesh -> clusters of <= 8 triangles; meshes of <= 16 triangles stay one flat list) sized for meshes of 2..1440 triangles.
 //
 // Geometry comes from the reference's data directory when one is given (the six OBJ files
 // the reference loads); otherwise from this repo's own description of the same shapes: the
@@ -236,14 +236,14 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
     int meshFirstSub[M_COUNT], meshNumSub[M_COUNT];
     float meshAabb[M_COUNT][6];
     // single-cluster meshes first: their triangles are what the kernel stages in shared memory
-    auto isSmall = [&](int i) { return src[i].subs.size() == 1 && (int)src[i].subs[0].tris.size() <= kViewClusterTris; };
+    auto isSmall = [&](int i) { return src[i].subs.size() == 1 && (int)src[i].subs[0].tris.size() <= kViewSmallTris; };
     std::vector<int> order;
     for (int i = 0; i < M_COUNT; i++) if (isSmall(i)) order.push_back(i);
     const size_t numSmallMeshes = order.size();
     for (int i = 0; i < M_COUNT; i++) if (!isSmall(i)) order.push_back(i);
     for (size_t oi = 0; oi < order.size(); oi++) {
         const int i = order[oi];
-        if (oi == numSmallMeshes) T.numSmallTris = T.numTris <= kViewSmallTris ? T.numTris : 0;
+        if (oi == numSmallMeshes) T.numSmallTris = T.numTris;
         MeshSrc &m = src[i];
         if ((int)m.subs.size() > kViewMaxSubPerObj || T.numSub + (int)m.subs.size() > kViewMaxSubmeshes) {
             g_viewErr = "render mesh has too many submeshes";
@@ -254,8 +254,9 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
         for (int k = 0; k < 3; k++) { meshAabb[i][k] = FLT_MAX; meshAabb[i][3 + k] = -FLT_MAX; }
         for (SubSrc &s : m.subs) {
             std::vector<std::pair<int, int>> cl;
-            splitClusters(s.tris, 0, (int)s.tris.size(), cl);
-            if (cl.size() > 32) { g_viewErr = "render submesh needs more than 32 clusters"; return g_viewErr.c_str(); }
+            if (isSmall(i)) cl.push_back({0, (int)s.tris.size()});      // one flat list
+            else splitClusters(s.tris, 0, (int)s.tris.size(), cl);
+            if (cl.size() > 64) { g_viewErr = "render submesh needs more than 64 clusters"; return g_viewErr.c_str(); }
             if (T.numClusters + (int)cl.size() > kViewMaxClusters || T.numTris + (int)s.tris.size() > kViewMaxTris) {
                 g_viewErr = "render meshes exceed the view table capacity";
                 return g_viewErr.c_str();
@@ -277,7 +278,7 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
             for (const Tri &t : s.tris) std::memcpy(T.tri[T.numTris++], t.v, sizeof(t.v));
         }
     }
-    if (numSmallMeshes == order.size()) T.numSmallTris = T.numTris <= kViewSmallTris ? T.numTris : 0;
+    if (numSmallMeshes == order.size()) T.numSmallTris = T.numTris;
     // the cluster / submesh boxes cull in object space: pad them like the instance boxes
     auto pad = [](ViewBox &b) {
         for (int k = 0; k < 3; k++) {

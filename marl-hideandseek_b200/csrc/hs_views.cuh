@@ -27,13 +27,14 @@
 
 namespace hs {
 
-constexpr int kViewMaxTris = 1600;
-constexpr int kViewMaxClusters = 160;
+constexpr int kViewMaxTris = 1552;
+constexpr int kViewMaxClusters = 200;
 constexpr int kViewMaxSubmeshes = 16;
 constexpr int kViewMaxSubPerObj = 3;
-constexpr int kViewClusterTris = 16;
+constexpr int kViewClusterTris = 8;       // <= 64 clusters per submesh (one 64-bit mask)
 constexpr int kViewThreads = 256;
-constexpr int kViewSmallTris = 64;     // triangles of the single-cluster meshes, staged in shared memory
+constexpr int kViewSmallTris = 16;     // a mesh of at most this many triangles is one flat list with a 16-bit facing mask
+constexpr int kViewCtasPerSm = 3;
 
 struct ViewBox { float lo[3]; int first; float hi[3]; int count; };     // 32 B
 struct ViewMeshTable {
@@ -43,7 +44,7 @@ struct ViewMeshTable {
     ViewBox sub[kViewMaxSubmeshes];                    // first/count index clusters
     ViewBox cluster[kViewMaxClusters];                 // first/count index triangles
     int numSub, numClusters, numTris;
-    int numSmallTris;                                  // tri[0, numSmallTris): single-cluster meshes, stored first
+    int numSmallTris;                                  // tri[0, numSmallTris): the single-cluster meshes, stored first
     float fovScale;                                    // 1 / tanf(toRadians(100 / 2))
     float tri[kViewMaxTris][9];                        // a, b, c in object space
 };
@@ -67,15 +68,14 @@ struct ViewInst {
     // `mask` = the subset that faces the camera.  triCount == 0 marks a clustered mesh.
     int triFirst, triCount;
     // clustered meshes (agents): per submesh, the clusters holding a triangle that faces the camera
-    uint32_t cmask[kViewMaxSubPerObj];
+    unsigned long long cmask[kViewMaxSubPerObj];
 };
 
 struct ViewSmem {
     ViewInst inst[kMaxBodies];           // front to back by distance from the camera to the box
     float key[kMaxBodies];
-    float tri[kViewSmallTris][9];
-    int numInst;                         // instances worth visiting (skipped ones sort last)
     int active;
+    int nextTile;                        // tiles are handed to the warps dynamically (their cost varies a lot)
     Vec3 origin, lowerLeft, horizontal, vertical;
 };
 
@@ -153,20 +153,29 @@ __device__ __forceinline__ bool viewBoxBehind(Vec3 n, Vec3 lo, Vec3 hi)
     return m < 0.f;
 }
 
-// One CTA per view (world, agent slot); a warp shades 8x4 pixel tiles.
-__global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, ViewParams P)
+// Persistent CTAs (kViewCtasPerSm per SM): the whole render-mesh table (64 KB) is copied into
+// shared memory once per CTA, then the CTA takes views (world, agent slot) round-robin; a warp
+// shades 8x4 pixel tiles.
+__global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(DeviceState S, ViewParams P, int numViews)
 {
     __shared__ ViewSmem sm;
-    const int A = S.p.agentsPerWorld;
-    const int view = blockIdx.x;
-    const int w = view / A, k = view - w * A;
-    const int W = P.width, H = P.height;
-    const ViewMeshTable &M = *P.mesh;
+    extern __shared__ uint4 viewMeshSmem[];
+    const ViewMeshTable &M = *reinterpret_cast<const ViewMeshTable *>(viewMeshSmem);
     const int tid = threadIdx.x;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(P.mesh);
+        for (int i = tid; i < int(sizeof(ViewMeshTable) / sizeof(uint4)); i += kViewThreads) viewMeshSmem[i] = src[i];
+    }
+    const int A = S.p.agentsPerWorld;
+    const int W = P.width, H = P.height;
+  for (int view = blockIdx.x; view < numViews; view += gridDim.x) {
+    const int w = view / A, k = view - w * A;
+    __syncthreads();         // the table copy (first round) / the previous view's readers of sm
 
     if (tid == 0) {
         int slot = WB(S, WB_IFACE_SLOT + k, w);
         sm.active = slot != 0xFF;
+        sm.nextTile = 0;
         if (sm.active) {
             // viewTransformUpdate + calculateOutRay
             Pose ps = loadPose(S, REC_POSE, slot, w);
@@ -182,7 +191,6 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
             sm.lowerLeft = start - sm.horizontal / 2.f - sm.vertical / 2.f + forward;
         }
     }
-    for (int i = tid; i < M.numSmallTris * 9; i += kViewThreads) (&sm.tri[0][0])[i] = (&M.tri[0][0])[i];
     __syncthreads();
     const size_t pixBase = size_t(view) * W * H;
     if (!sm.active) {
@@ -190,7 +198,7 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
             P.depth[pixBase + i] = 0.f;
             reinterpret_cast<uint32_t *>(P.rgb)[pixBase + i] = 0u;
         }
-        return;
+        continue;
     }
     const int nBodies = WI(S, WF_NUM_BODIES, w);
     ViewInst I;
@@ -221,10 +229,10 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
         if (!skip && M.objNumSub[obj] == 1) {
             const ViewBox &SB = M.sub[M.objFirstSub[obj]];
             const ViewBox &CB = M.cluster[SB.first];
-            if (SB.count == 1 && CB.first + CB.count <= M.numSmallTris) {
+            if (SB.count == 1 && CB.count <= kViewSmallTris) {
                 I.triFirst = CB.first; I.triCount = CB.count;
                 for (int t = 0; t < CB.count; t++)
-                    if (viewFacesCamera(sm.tri[CB.first + t], I.ro)) I.mask |= 1u << t;
+                    if (viewFacesCamera(M.tri[CB.first + t], I.ro)) I.mask |= 1u << t;
                 if (I.mask == 0) skip = true;
             }
         }
@@ -244,7 +252,6 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
         }
         sm.inst[rank] = I;
     }
-    if (tid == 0) sm.numInst = live;
     __syncthreads();
     const int nInst = live;
     // clustered instances: thread per cluster marks the clusters with a camera-facing triangle
@@ -260,17 +267,21 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
                 const ViewBox &CB = M.cluster[SB.first + c];
                 bool any = false;
                 for (int t = 0; t < CB.count; t++) any |= viewFacesCamera(M.tri[CB.first + t], ro);
-                if (any) atomicOr(&sm.inst[i].cmask[s], 1u << c);
+                if (any) atomicOr(&sm.inst[i].cmask[s], 1ull << c);
             }
         }
     }
     __syncthreads();
 
-    const int warp = tid >> 5, lane = tid & 31;
+    const int lane = tid & 31;
     const int tilesX = (W + 7) / 8, tilesY = (H + 3) / 4;
     const Vec3 o = sm.origin;
     const Vec3 LL = sm.lowerLeft - o, HZ = sm.horizontal, VT = sm.vertical;
-    for (int tile = warp; tile < tilesX * tilesY; tile += kViewThreads / 32) {
+    for (;;) {
+        int tile = 0;
+        if (lane == 0) tile = atomicAdd(&sm.nextTile, 1);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= tilesX * tilesY) break;
         const int px0 = (tile % tilesX) * 8, py0 = (tile / tilesX) * 4;
         // Warp-cooperative cull: lane j tests instances j and j+32 against the pyramid of this
         // 8x4-pixel tile (apex = camera, four side planes through the tile's corner rays); the
@@ -325,7 +336,7 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
             if (triCount > 0) {
                 const int first = sm.inst[i].triFirst;
                 for (uint32_t m = sm.inst[i].mask; m; m &= m - 1) {
-                    float th = woopHit(sm.tri[first + __ffs(m) - 1], R, tmax);
+                    float th = woopHit(M.tri[first + __ffs(m) - 1], R, tmax);
                     if (th >= 0.f) { tmax = th; hit = true; hitSub = 0; }
                 }
             } else {
@@ -333,12 +344,12 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
                 const int obj = sm.inst[i].obj;
                 const int s0 = M.objFirstSub[obj], ns = M.objNumSub[obj];
                 for (int s = 0; s < ns; s++) {
-                    uint32_t cm = sm.inst[i].cmask[s];
+                    unsigned long long cm = sm.inst[i].cmask[s];
                     if (cm == 0) continue;
                     const ViewBox &SB = M.sub[s0 + s];
                     if (ns > 1 && !viewSlab(SB.lo, SB.hi, ro, invrd, tmax)) continue;
                     for (; cm; cm &= cm - 1) {
-                        const ViewBox &CB = M.cluster[SB.first + __ffs(cm) - 1];
+                        const ViewBox &CB = M.cluster[SB.first + __ffsll((long long)cm) - 1];
                         if (!viewSlab(CB.lo, CB.hi, ro, invrd, tmax)) continue;
                         for (int t = 0; t < CB.count; t++) {
                             float th = woopHit(M.tri[CB.first + t], R, tmax);
@@ -364,6 +375,7 @@ __global__ void __launch_bounds__(kViewThreads, 3) k_agent_views(DeviceState S, 
         P.depth[pix] = depth;
         reinterpret_cast<uint32_t *>(P.rgb)[pix] = rgba;
     }
+  }
 }
 
 #endif  // __CUDACC__

@@ -29,6 +29,6 @@ world_dt = np.dtype([
 view_box_dt = np.dtype([("lo", "f4", 3), ("first", "i4"), ("hi", "f4", 3), ("count", "i4")])
 view_mesh_dt = np.dtype([
     ("obj_first_sub", "i4", 8), ("obj_num_sub", "i4", 8), ("obj_aabb", "f4", (8, 6)),
-    ("sub_color", "f4", (8, 3, 3)), ("sub", view_box_dt, 16), ("cluster", view_box_dt, 160),
+    ("sub_color", "f4", (8, 3, 3)), ("sub", view_box_dt, 16), ("cluster", view_box_dt, 200),
     ("num_sub", "i4"), ("num_clusters", "i4"), ("num_tris", "i4"), ("num_small_tris", "i4"),
-    ("fov_scale", "f4"), ("tri", "f4", (1600, 9))])
+    ("fov_scale", "f4"), ("tri", "f4", (1552, 9))])

@@ -110,7 +110,7 @@ def test_builtin_meshes_match_reference_objs():
 def test_table_capacity_and_clusters():
     for d in ([None, vu.REF_DATA] if vu.have_ref_data() else [None]):
         t = table(d)
-        assert t["num_tris"] <= 1600 and t["num_clusters"] <= 160 and t["num_sub"] <= 16
+        assert t["num_tris"] <= 1552 and t["num_clusters"] <= 200 and t["num_sub"] <= 16
         # every triangle lies inside its cluster box, every cluster inside its submesh box
         for s in range(int(t["num_sub"])):
             sb = t["sub"][s]
