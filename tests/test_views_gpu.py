@@ -125,3 +125,28 @@ def test_views_sharding_invariance_full_shard():
     assert torch.equal(big.rgb_tensor().to_torch()[base * A:(base + 64) * A], small.rgb_tensor().to_torch())
     assert torch.equal(small.self_data_tensor().to_torch(), plain.self_data_tensor().to_torch())
     assert (ds.flatten(1).amax(1) > 0).all()
+
+
+def test_benchmark_script_call_sequence():
+    """scripts/benchmark.py of the reference, call for call (constructor keywords :20-35, tensors
+    :38-47, loop :64-88), at a reduced world count: it must run unmodified against this module."""
+    import gpu_hideseek
+    num_worlds, num_steps, gpu_id = 1024, 12, 0
+    sim = gpu_hideseek.HideAndSeekSimulator(
+        exec_mode=gpu_hideseek.madrona.ExecMode.CUDA, gpu_id=gpu_id, num_worlds=num_worlds, sim_flags=0,
+        rand_seed=0, min_hiders=2, max_hiders=2, min_seekers=2, max_seekers=2, num_pbt_policies=1,
+        enable_batch_renderer=True, batch_render_width=64, batch_render_height=64)
+    sim.init()
+    actions = sim.action_tensor().to_torch()
+    resets = sim.reset_tensor().to_torch()
+    assert actions.shape == (num_worlds * 4, 5) and resets.shape == (num_worlds, 1)
+    rgb_observations = sim.rgb_tensor().to_torch()
+    assert rgb_observations.shape == (num_worlds * 4, 64, 64, 4) and rgb_observations.dtype == torch.uint8
+    first = rgb_observations.clone()
+    for i in range(5 + num_steps):
+        sim.step()
+        actions[..., 0] = torch.randint_like(actions[..., 0], -5, 5)
+        actions[..., 1] = torch.randint_like(actions[..., 1], -5, 5)
+    assert not torch.equal(first, rgb_observations)            # the zero-copy view follows the simulation
+    assert (rgb_observations[..., 3] == 255).all()
+    del sim
