@@ -487,7 +487,7 @@ extern "C" int hs_enable_views(hs_sim *sim, int width, int height, const char *d
     if (width <= 0 || height <= 0 || width > 4096 || height > 4096) { g_err = "hs_enable_views: invalid view size"; return 1; }
     HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
     if (!data_dir || !data_dir[0]) data_dir = getenv("HIDESEEK_DATA_DIR");
-    sim->viewMeshHost = new ViewMeshTable();
+    if (!sim->viewMeshHost) sim->viewMeshHost = new ViewMeshTable();
     const char *err = buildViewMeshTable(*sim->viewMeshHost, data_dir);
     if (err[0]) { g_err = std::string("hs_enable_views: ") + err; return 1; }
     ViewMeshTable *dev = nullptr;
