@@ -127,8 +127,8 @@ void hs_xla_gpu_load_checkpoints(void *stream, void **buffers, const char *opaqu
  * The Vulkan rasteriser is unavailable here; this is a CUDA ray caster with the arithmetic of
  * Madrona's software ray caster (M/src/mw/device/bvh_raycast.cpp) — see csrc/hs_views.cuh.
  *   hs_enable_views: call once between hs_create and hs_init.  `data_dir` = the reference's
- *     data/ directory (render OBJ meshes, src/mgr.cpp:590-609); NULL/"" = $HIDESEEK_DATA_DIR,
- *     else built-in meshes.  Allocates [N*A,H,W,1] f32 depth and [N*A,H,W,4] u8 RGBA.
+ *     data/ directory (render OBJ meshes and the three PNG textures, src/mgr.cpp:590-665);
+ *     NULL/"" = $HIDESEEK_DATA_DIR, else built-in meshes without textures.  Allocates [N*A,H,W,1] f32 depth and [N*A,H,W,4] u8 RGBA.
  *   hs_render_views: renders every agent slot's view of the current state on `stream`
  *     (asynchronous); the Manager calls it after hs_init / hs_step like the reference.
  *   hs_export(HS_EXPORT_VIEW_DEPTH / HS_EXPORT_VIEW_RGB) returns the two tensors.
@@ -138,6 +138,8 @@ int hs_enable_views(hs_sim *sim, int width, int height, const char *data_dir);
 int hs_render_views(hs_sim *sim, void *stream);
 int hs_view_mesh_table_bytes(void);
 int hs_build_view_mesh_table(const char *data_dir, void *out, int out_bytes);
+int hs_view_tex_table_bytes(void);       /* hs::ViewTexTable: per-triangle UVs, material -> texture */
+int hs_build_view_tex_table(const char *data_dir, void *out, int out_bytes);
 
 /* Diagnostics / parity: flat per-world internal state (layout in
  * hideseek/debug_dump.h), number of kernels launched by the last hs_step,

@@ -30,6 +30,7 @@
 
 namespace hs {
 void buildAssetTable(AssetTable &T);
+const char *decodePngRGBA(const char *path, int *width, int *height, std::vector<uint8_t> &rgba);   // hs_view_assets.cpp
 cudaError_t launchAgentViews(const DeviceState &S, const ViewParams &P, unsigned views, cudaStream_t stream);   // hs_views.cu
 }
 
@@ -65,6 +66,8 @@ struct hs_sim {
     bool viewsEnabled = false;
     ViewParams view{};
     ViewMeshTable *viewMeshHost = nullptr;
+    ViewTexTable *viewTexHost = nullptr;
+    cudaArray_t viewTexArray[kViewTextures] = {};
 };
 
 template <typename T>
@@ -224,7 +227,13 @@ extern "C" void hs_destroy(hs_sim *sim)
         if (sim->joinEvent[b]) cudaEventDestroy(sim->joinEvent[b]);
     }
     for (void *p : sim->allocs) cudaFree(p);
+    if (sim->viewTexHost)
+        for (int i = 0; i < kViewTextures; i++) {
+            if (sim->viewTexHost->tex[i]) cudaDestroyTextureObject((cudaTextureObject_t)sim->viewTexHost->tex[i]);
+            if (sim->viewTexArray[i]) cudaFreeArray(sim->viewTexArray[i]);
+        }
     delete sim->viewMeshHost;
+    delete sim->viewTexHost;
     delete sim;
 }
 
@@ -488,11 +497,43 @@ extern "C" int hs_enable_views(hs_sim *sim, int width, int height, const char *d
     HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
     if (!data_dir || !data_dir[0]) data_dir = getenv("HIDESEEK_DATA_DIR");
     if (!sim->viewMeshHost) sim->viewMeshHost = new ViewMeshTable();
-    const char *err = buildViewMeshTable(*sim->viewMeshHost, data_dir);
+    if (!sim->viewTexHost) sim->viewTexHost = new ViewTexTable();
+    const char *err = buildViewMeshTable(*sim->viewMeshHost, *sim->viewTexHost, data_dir);
     if (err[0]) { g_err = std::string("hs_enable_views: ") + err; return 1; }
+    if (data_dir && data_dir[0]) {
+        // the three textures of loadRenderObjects (src/mgr.cpp:649-665) as CUDA texture objects
+        // configured like the reference's (M/src/render/asset_processor.cpp:312-349)
+        const char *names[kViewTextures] = {"green_grid.png", "smile.png", "red_smile.png"};
+        for (int i = 0; i < kViewTextures; i++) {
+            int w = 0, h = 0;
+            std::vector<uint8_t> rgba;
+            err = decodePngRGBA((std::string(data_dir) + "/" + names[i]).c_str(), &w, &h, rgba);
+            if (err[0]) { g_err = std::string("hs_enable_views: ") + err; return 1; }
+            cudaChannelFormatDesc ch = cudaCreateChannelDesc<uchar4>();
+            HS_CUDA(cudaMallocArray(&sim->viewTexArray[i], &ch, w, h, cudaArrayDefault));
+            HS_CUDA(cudaMemcpy2DToArray(sim->viewTexArray[i], 0, 0, rgba.data(), sizeof(uint32_t) * w, sizeof(uint32_t) * w, h,
+                                        cudaMemcpyHostToDevice));
+            cudaResourceDesc res = {};
+            res.resType = cudaResourceTypeArray;
+            res.res.array.array = sim->viewTexArray[i];
+            cudaTextureDesc td = {};
+            td.addressMode[0] = cudaAddressModeWrap;
+            td.addressMode[1] = cudaAddressModeWrap;
+            td.filterMode = cudaFilterModeLinear;
+            td.readMode = cudaReadModeNormalizedFloat;
+            td.normalizedCoords = 1;
+            cudaTextureObject_t obj = 0;
+            HS_CUDA(cudaCreateTextureObject(&obj, &res, &td, nullptr));
+            sim->viewTexHost->tex[i] = (unsigned long long)obj;
+        }
+    }
     ViewMeshTable *dev = nullptr;
     HS_TRY(devAlloc(sim, &dev, 1));
     HS_CUDA(cudaMemcpy(dev, sim->viewMeshHost, sizeof(ViewMeshTable), cudaMemcpyHostToDevice));
+    ViewTexTable *devTex = nullptr;
+    HS_TRY(devAlloc(sim, &devTex, 1));
+    HS_CUDA(cudaMemcpy(devTex, sim->viewTexHost, sizeof(ViewTexTable), cudaMemcpyHostToDevice));
+    sim->view.texTable = devTex;
     const size_t pixels = size_t(sim->cfg.num_worlds) * sim->S.p.agentsPerWorld * width * height;
     HS_TRY(devAlloc(sim, &sim->view.depth, pixels));
     HS_TRY(devAlloc(sim, &sim->view.rgb, pixels * 4));
@@ -520,8 +561,25 @@ extern "C" int hs_build_view_mesh_table(const char *data_dir, void *out, int out
 {
     if (!out || out_bytes != (int)sizeof(ViewMeshTable)) { g_err = "hs_build_view_mesh_table: bad buffer"; return 1; }
     if (!data_dir || !data_dir[0]) data_dir = getenv("HIDESEEK_DATA_DIR");
-    const char *err = buildViewMeshTable(*(ViewMeshTable *)out, data_dir);
+    ViewTexTable *X = new ViewTexTable();
+    const char *err = buildViewMeshTable(*(ViewMeshTable *)out, *X, data_dir);
+    delete X;
     if (err[0]) { g_err = std::string("hs_build_view_mesh_table: ") + err; return 1; }
+    return 0;
+}
+
+extern "C" int hs_view_tex_table_bytes(void) { return (int)sizeof(ViewTexTable); }
+
+// host-only: per-triangle texture coordinates and material -> texture bindings for `data_dir`
+// (the texture-object handles stay 0: they only exist inside a simulator)
+extern "C" int hs_build_view_tex_table(const char *data_dir, void *out, int out_bytes)
+{
+    if (!out || out_bytes != (int)sizeof(ViewTexTable)) { g_err = "hs_build_view_tex_table: bad buffer"; return 1; }
+    if (!data_dir || !data_dir[0]) data_dir = getenv("HIDESEEK_DATA_DIR");
+    ViewMeshTable *T = new ViewMeshTable();
+    const char *err = buildViewMeshTable(*T, *(ViewTexTable *)out, data_dir);
+    delete T;
+    if (err[0]) { g_err = std::string("hs_build_view_tex_table: ") + err; return 1; }
     return 0;
 }
 

@@ -22,11 +22,13 @@
 #include <string>
 #include <vector>
 
+#include <zlib.h>
+
 namespace hs {
 
 namespace {
 
-struct Tri { float v[9]; };
+struct Tri { float v[9]; float uv[6]; };
 struct SubSrc { std::vector<Tri> tris; };
 struct MeshSrc { std::vector<SubSrc> subs; };
 
@@ -34,6 +36,7 @@ Tri mkTri(const float *a, const float *b, const float *c)
 {
     Tri t;
     for (int k = 0; k < 3; k++) { t.v[k] = a[k]; t.v[3 + k] = b[k]; t.v[6 + k] = c[k]; }
+    for (int k = 0; k < 6; k++) t.uv[k] = 0.f;
     return t;
 }
 
@@ -140,12 +143,13 @@ MeshSrc agentStandIn()
     return m;
 }
 
-// minimal OBJ reader: `o` starts a submesh, `v` positions, `f` polygons (fan-triangulated)
+// minimal OBJ reader: `o` starts a submesh, `v` positions, `vt` texture coordinates,
+// `f` polygons of v[/vt[/vn]] corners (fan-triangulated)
 bool loadObj(const std::string &path, MeshSrc &m, std::string &err)
 {
     FILE *fp = fopen(path.c_str(), "r");
     if (!fp) { err = "cannot open " + path; return false; }
-    std::vector<float> pos;
+    std::vector<float> pos, tex;
     char line[512];
     m.subs.clear();
     while (fgets(line, sizeof(line), fp)) {
@@ -155,17 +159,32 @@ bool loadObj(const std::string &path, MeshSrc &m, std::string &err)
             if (sscanf(line + 2, "%f %f %f", &x, &y, &z) == 3) { pos.push_back(x); pos.push_back(y); pos.push_back(z); }
             continue;
         }
+        if (line[0] == 'v' && line[1] == 't' && line[2] == ' ') {
+            float u, v;
+            if (sscanf(line + 3, "%f %f", &u, &v) == 2) { tex.push_back(u); tex.push_back(v); }
+            continue;
+        }
         if (line[0] == 'f' && line[1] == ' ') {
             if (m.subs.empty()) m.subs.emplace_back();
-            std::vector<int> idx;
+            std::vector<int> idx, tidx;
             for (char *p = strtok(line + 2, " \t\r\n"); p; p = strtok(nullptr, " \t\r\n")) {
                 int i = atoi(p);
                 if (i < 0) i = (int)pos.size() / 3 + i + 1;
                 if (i <= 0 || i > (int)pos.size() / 3) { fclose(fp); err = "bad face index in " + path; return false; }
                 idx.push_back(i - 1);
+                int t = 0;
+                if (const char *sl = strchr(p, '/')) t = atoi(sl + 1);
+                if (t < 0) t = (int)tex.size() / 2 + t + 1;
+                if (t > (int)tex.size() / 2) { fclose(fp); err = "bad texture index in " + path; return false; }
+                tidx.push_back(t - 1);
             }
-            for (size_t k = 1; k + 1 < idx.size(); k++)
-                m.subs.back().tris.push_back(mkTri(&pos[3 * idx[0]], &pos[3 * idx[k]], &pos[3 * idx[k + 1]]));
+            for (size_t k = 1; k + 1 < idx.size(); k++) {
+                Tri t = mkTri(&pos[3 * idx[0]], &pos[3 * idx[k]], &pos[3 * idx[k + 1]]);
+                const size_t corner[3] = {0, k, k + 1};
+                for (int c = 0; c < 3; c++)
+                    if (tidx[corner[c]] >= 0) { t.uv[2 * c] = tex[2 * tidx[corner[c]]]; t.uv[2 * c + 1] = tex[2 * tidx[corner[c]] + 1]; }
+                m.subs.back().tris.push_back(t);
+            }
         }
     }
     fclose(fp);
@@ -210,11 +229,82 @@ float srgbToLinear(float s)      // M/include/madrona/render/common.inl:3-10
 
 std::string g_viewErr;
 
+uint32_t be32(const uint8_t *p) { return (uint32_t(p[0]) << 24) | (uint32_t(p[1]) << 16) | (uint32_t(p[2]) << 8) | p[3]; }
+
 }  // namespace
 
-const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
+// 8-bit RGB / RGBA, non-interlaced PNG -> RGBA8 rows top to bottom (what the reference's image
+// importer hands to cudaMemcpy2DToArray, M/src/render/asset_processor.cpp:312-331).
+const char *decodePngRGBA(const char *path, int *width, int *height, std::vector<uint8_t> &rgba)
+{
+    g_viewErr.clear();
+    FILE *fp = fopen(path, "rb");
+    if (!fp) { g_viewErr = std::string("cannot open ") + path; return g_viewErr.c_str(); }
+    std::vector<uint8_t> file;
+    uint8_t buf[65536];
+    for (size_t n; (n = fread(buf, 1, sizeof(buf), fp)) > 0;) file.insert(file.end(), buf, buf + n);
+    fclose(fp);
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    if (file.size() < 8 || memcmp(file.data(), sig, 8) != 0) { g_viewErr = std::string("not a PNG: ") + path; return g_viewErr.c_str(); }
+    int w = 0, h = 0, channels = 0;
+    std::vector<uint8_t> idat;
+    for (size_t off = 8; off + 12 <= file.size();) {
+        uint32_t len = be32(&file[off]);
+        const uint8_t *type = &file[off + 4], *data = &file[off + 8];
+        if (off + 12 + len > file.size()) break;
+        if (!memcmp(type, "IHDR", 4)) {
+            w = (int)be32(data); h = (int)be32(data + 4);
+            const int depth = data[8], color = data[9], interlace = data[12];
+            channels = color == 6 ? 4 : (color == 2 ? 3 : 0);
+            if (depth != 8 || channels == 0 || interlace != 0) { g_viewErr = std::string("unsupported PNG format: ") + path; return g_viewErr.c_str(); }
+        } else if (!memcmp(type, "IDAT", 4)) {
+            idat.insert(idat.end(), data, data + len);
+        } else if (!memcmp(type, "IEND", 4)) {
+            break;
+        }
+        off += 12 + len;
+    }
+    if (w <= 0 || h <= 0 || idat.empty()) { g_viewErr = std::string("truncated PNG: ") + path; return g_viewErr.c_str(); }
+    const size_t stride = size_t(w) * channels;
+    std::vector<uint8_t> raw((stride + 1) * h);
+    uLongf rawLen = (uLongf)raw.size();
+    if (uncompress(raw.data(), &rawLen, idat.data(), (uLong)idat.size()) != Z_OK || rawLen != raw.size()) {
+        g_viewErr = std::string("PNG inflate failed: ") + path;
+        return g_viewErr.c_str();
+    }
+    // undo the per-row filters (PNG spec 9.2) in place
+    std::vector<uint8_t> prev(stride, 0);
+    rgba.assign(size_t(w) * h * 4, 255);
+    for (int y = 0; y < h; y++) {
+        const int filter = raw[(stride + 1) * y];
+        uint8_t *row = &raw[(stride + 1) * y + 1];
+        for (size_t i = 0; i < stride; i++) {
+            const int a = i >= (size_t)channels ? row[i - channels] : 0, b = prev[i];
+            const int c = i >= (size_t)channels ? prev[i - channels] : 0;
+            int pred = 0;
+            switch (filter) {
+            case 1: pred = a; break;
+            case 2: pred = b; break;
+            case 3: pred = (a + b) / 2; break;
+            case 4: { int p = a + b - c, pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+                      pred = (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c); } break;
+            default: break;
+            }
+            row[i] = uint8_t(row[i] + pred);
+        }
+        memcpy(prev.data(), row, stride);
+        for (int x = 0; x < w; x++)
+            for (int k = 0; k < channels; k++) rgba[(size_t(y) * w + x) * 4 + k] = row[size_t(x) * channels + k];
+    }
+    *width = w; *height = h;
+    return "";
+}
+
+const char *buildViewMeshTable(ViewMeshTable &T, ViewTexTable &X, const char *dataDir)
 {
     std::memset(&T, 0, sizeof(T));
+    std::memset(&X, 0, sizeof(X));
+    for (int o = 0; o < OBJ_COUNT; o++) for (int k = 0; k < kViewMaxSubPerObj; k++) X.subTex[o][k] = -1;
     g_viewErr.clear();
     // distinct meshes; Hider and Seeker share one
     enum { M_PLANE, M_CUBE, M_WALL, M_AGENT, M_RAMP, M_BOX, M_COUNT };
@@ -275,7 +365,10 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
                 CB.count = c.second;
                 boundsOf(s.tris.data() + c.first, c.second, CB.lo, CB.hi);
             }
-            for (const Tri &t : s.tris) std::memcpy(T.tri[T.numTris++], t.v, sizeof(t.v));
+            for (const Tri &t : s.tris) {
+                std::memcpy(X.triUV[T.numTris], t.uv, sizeof(t.uv));
+                std::memcpy(T.tri[T.numTris++], t.v, sizeof(t.v));
+            }
         }
     }
     if (numSmallMeshes == order.size()) T.numSmallTris = T.numTris;
@@ -308,6 +401,13 @@ const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir)
         std::memcpy(T.objAabb[b.obj], meshAabb[b.mesh], sizeof(float) * 6);
         for (int s = 0; s < kViewMaxSubPerObj; s++)
             for (int k = 0; k < 3; k++) T.subColor[b.obj][s][k] = b.col[s][k];
+    }
+    // textures (src/mgr.cpp:624-665): image 0 green_grid -> the ground, 1 smile -> hider body,
+    // 2 red_smile -> seeker body; only with the reference's data directory (UVs come from its OBJs)
+    if (dataDir && dataDir[0]) {
+        X.subTex[OBJ_PLANE][0] = 0;
+        X.subTex[OBJ_HIDER][0] = 1;
+        X.subTex[OBJ_SEEKER][0] = 2;
     }
     // attachEntityToView(..., 100.f, ...) -> fov_scale (M/src/render/ecs_system.cpp:655-660)
     const float toRad = 3.14159265358979323846f / 180.f;

@@ -19,8 +19,10 @@
 // so far, then the mesh's triangles).  Which triangles of a box / wedge / ground instance face
 // the camera is decided once per view, not per pixel.  This file is its own translation unit
 // (hs_views.cu) compiled with FMA contraction on: nothing here has to match a CPU bit for bit.
-// Texture lookups (plane grid, agent faces) are not reproduced: textured materials use their
-// base colour.  Inactive agent slots produce an all-zero view.
+// The three textures (ground grid, hider / seeker faces) are sampled through CUDA texture
+// objects set up like the reference's when a data directory is given; the built-in meshes have
+// no texture coordinates and use the material's base colour.  Inactive agent slots produce an
+// all-zero view.
 #pragma once
 
 #include "hs_state.cuh"
@@ -49,8 +51,18 @@ struct ViewMeshTable {
     float tri[kViewMaxTris][9];                        // a, b, c in object space
 };
 
+// What only the final shading of a pixel needs (stays in global memory): texture coordinates of
+// every triangle, and which texture a (object, submesh) material samples (-1: base colour only).
+constexpr int kViewTextures = 3;
+struct ViewTexTable {
+    float triUV[kViewMaxTris][6];
+    int subTex[OBJ_COUNT][kViewMaxSubPerObj];
+    unsigned long long tex[kViewTextures];             // cudaTextureObject_t: RGBA8, wrap, linear, normalised
+};
+
 struct ViewParams {
     const ViewMeshTable *mesh;
+    const ViewTexTable *texTable;
     float *depth;            // [N*A, H, W, 1]
     uint8_t *rgb;            // [N*A, H, W, 4]
     int width, height;
@@ -127,6 +139,33 @@ __device__ __forceinline__ float woopHit(const float *t9, const WoopRay &R, floa
     float T = fmaf(U, Az, fmaf(V, Bz, W * Cz));
     if (T < 0.f || T > t_max * det) return -1.f;
     return T * (1.f / det);
+}
+
+// Normalised barycentrics (U, V, W) / det of a triangle the ray is known to hit — the same
+// arithmetic as woopHit up to the determinant (bvh_raycast.cpp:331-392, 436-439); used once per
+// pixel to interpolate the texture coordinates of the final hit (triangleIntersect :474-476).
+__device__ __forceinline__ Vec3 woopBary(const float *t9, const WoopRay &R)
+{
+    const float a_kx = t9[R.kx] - R.ox, a_ky = t9[R.ky] - R.oy, a_kz = t9[R.kz] - R.oz;
+    const float b_kx = t9[3 + R.kx] - R.ox, b_ky = t9[3 + R.ky] - R.oy, b_kz = t9[3 + R.kz] - R.oz;
+    const float c_kx = t9[6 + R.kx] - R.ox, c_ky = t9[6 + R.ky] - R.oy, c_kz = t9[6 + R.kz] - R.oz;
+    float Ax = fmaf(-R.Sx, a_kz, a_kx), Ay = fmaf(-R.Sy, a_kz, a_ky);
+    float Bx = fmaf(-R.Sx, b_kz, b_kx), By = fmaf(-R.Sy, b_kz, b_ky);
+    float Cx = fmaf(-R.Sx, c_kz, c_kx), Cy = fmaf(-R.Sy, c_kz, c_ky);
+    float U = fmaf(Cx, By, -Cy * Bx);
+    float V = fmaf(Ax, Cy, -Ay * Cx);
+    float W = fmaf(Bx, Ay, -By * Ax);
+    const float eps = 1e-7f;
+    if (fabsf(U) < eps) U = 0.f;
+    if (fabsf(V) < eps) V = 0.f;
+    if (fabsf(W) < eps) W = 0.f;
+    if (U == 0.f || V == 0.f || W == 0.f) {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
+    const float rcp = 1.f / (U + V + W);
+    return {U * rcp, V * rcp, W * rcp};
 }
 
 __device__ __forceinline__ bool viewSlab(const float *lo, const float *hi, Vec3 o, Vec3 inv_d, float t_max)
@@ -321,7 +360,7 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
         Vec3 d = normalize(sm.lowerLeft + pu * sm.horizontal + pv * sm.vertical - o);
         Vec3 invd = {1.f / d.x, 1.f / d.y, 1.f / d.z};
         float best = 10000.f;
-        int hitObj = -1, hitSub = 0;
+        int hitObj = -1, hitSub = 0, hitInst = 0, hitTri = 0;
         for (; todo; todo &= todo - 1) {
             const int i = __ffsll((long long)todo) - 1;
             if (!aabbRayIntersects(sm.inst[i].lo, sm.inst[i].hi, o, invd, 0.f, best)) continue;
@@ -332,12 +371,14 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
             float tmax = best * ts;
             const WoopRay R = woopSetup(rd, ro);
             bool hit = false;
+            int tri = 0;
             const int triCount = sm.inst[i].triCount;
             if (triCount > 0) {
                 const int first = sm.inst[i].triFirst;
                 for (uint32_t m = sm.inst[i].mask; m; m &= m - 1) {
-                    float th = woopHit(M.tri[first + __ffs(m) - 1], R, tmax);
-                    if (th >= 0.f) { tmax = th; hit = true; hitSub = 0; }
+                    const int t = first + __ffs(m) - 1;
+                    float th = woopHit(M.tri[t], R, tmax);
+                    if (th >= 0.f) { tmax = th; hit = true; hitSub = 0; tri = t; }
                 }
             } else {
                 Vec3 invrd = {1.f / rd.x, 1.f / rd.y, 1.f / rd.z};
@@ -353,12 +394,12 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
                         if (!viewSlab(CB.lo, CB.hi, ro, invrd, tmax)) continue;
                         for (int t = 0; t < CB.count; t++) {
                             float th = woopHit(M.tri[CB.first + t], R, tmax);
-                            if (th >= 0.f) { tmax = th; hit = true; hitSub = s; }
+                            if (th >= 0.f) { tmax = th; hit = true; hitSub = s; tri = CB.first + t; }
                         }
                     }
                 }
             }
-            if (hit) { best = tmax / ts; hitObj = sm.inst[i].obj; }
+            if (hit) { best = tmax / ts; hitObj = sm.inst[i].obj; hitInst = i; hitTri = tri; }
         }
         const size_t pix = pixBase + size_t(py) * W + px;
         uint32_t rgba = 0xFF000000u;
@@ -366,10 +407,24 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
         if (hitObj >= 0) {
             depth = best;
             const float *col = M.subColor[hitObj][hitSub];
+            Vec3 c = {col[0], col[1], col[2]};
+            const int texId = P.texTable->subTex[hitObj][hitSub];
+            if (texId >= 0) {
+                // traceRay's material lookup (bvh_raycast.cpp:783-797): interpolate the hit
+                // triangle's texture coordinates, sample at (u, 1 - v), modulate the base colour
+                Vec3 rd = d.x * sm.inst[hitInst].cx + d.y * sm.inst[hitInst].cy + d.z * sm.inst[hitInst].cz;
+                rd = rd / length(rd);
+                const Vec3 bary = woopBary(M.tri[hitTri], woopSetup(rd, sm.inst[hitInst].ro));
+                const float *uv = P.texTable->triUV[hitTri];
+                const float tu = uv[0] * bary.x + uv[2] * bary.y + uv[4] * bary.z;
+                const float tv = uv[1] * bary.x + uv[3] * bary.y + uv[5] * bary.z;
+                const float4 tc = tex2D<float4>((cudaTextureObject_t)P.texTable->tex[texId], tu, 1.f - tv);
+                c = {tc.x * c.x, tc.y * c.y, tc.z * c.z};
+            }
             // acc_color = fmaxf(0.2, light_contrib = 0) * color, clamped to 1; bytes truncate
-            uint32_t r = (uint32_t)(fminf(1.f, 0.2f * col[0]) * 255.f);
-            uint32_t g = (uint32_t)(fminf(1.f, 0.2f * col[1]) * 255.f);
-            uint32_t b = (uint32_t)(fminf(1.f, 0.2f * col[2]) * 255.f);
+            uint32_t r = (uint32_t)(fminf(1.f, 0.2f * c.x) * 255.f);
+            uint32_t g = (uint32_t)(fminf(1.f, 0.2f * c.y) * 255.f);
+            uint32_t b = (uint32_t)(fminf(1.f, 0.2f * c.z) * 255.f);
             rgba |= r | (g << 8) | (b << 16);
         }
         P.depth[pix] = depth;
@@ -384,6 +439,6 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
 // (plane.obj, cube_render.obj, wall_render.obj, agent_render.obj, ramp_render.obj,
 // elongated_render.obj — src/mgr.cpp:590-609) or, with dataDir == nullptr, from built-in
 // descriptions of the same shapes.  Returns an empty string on success, else the error.
-const char *buildViewMeshTable(ViewMeshTable &T, const char *dataDir);
+const char *buildViewMeshTable(ViewMeshTable &T, ViewTexTable &X, const char *dataDir);
 
 }  // namespace hs

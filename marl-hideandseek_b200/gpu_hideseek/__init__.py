@@ -84,6 +84,7 @@ def load_library():
     l.hs_profiled_kernel_name.restype = C.c_char_p
     l.hs_world_stats.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
     l.hs_build_view_mesh_table.argtypes = [C.c_char_p, C.c_void_p, C.c_int]
+    l.hs_build_view_tex_table.argtypes = [C.c_char_p, C.c_void_p, C.c_int]
     _lib = l
     return l
 
@@ -101,6 +102,17 @@ def view_mesh_table(data_dir=None):
     out = np.zeros(1, dtype=view_mesh_dt)
     assert lib.hs_view_mesh_table_bytes() == view_mesh_dt.itemsize
     _check(lib.hs_build_view_mesh_table((data_dir or "").encode(), out.ctypes.data, view_mesh_dt.itemsize))
+    return out[0]
+
+
+def view_tex_table(data_dir=None):
+    """Per-triangle texture coordinates and material -> texture bindings of the agent views
+    (hs::ViewTexTable) for `data_dir`.  Host only."""
+    from .dump import view_tex_dt
+    lib = load_library()
+    out = np.zeros(1, dtype=view_tex_dt)
+    assert lib.hs_view_tex_table_bytes() == view_tex_dt.itemsize
+    _check(lib.hs_build_view_tex_table((data_dir or "").encode(), out.ctypes.data, view_tex_dt.itemsize))
     return out[0]
 
 

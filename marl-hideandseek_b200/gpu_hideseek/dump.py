@@ -32,3 +32,5 @@ view_mesh_dt = np.dtype([
     ("sub_color", "f4", (8, 3, 3)), ("sub", view_box_dt, 16), ("cluster", view_box_dt, 200),
     ("num_sub", "i4"), ("num_clusters", "i4"), ("num_tris", "i4"), ("num_small_tris", "i4"),
     ("fov_scale", "f4"), ("tri", "f4", (1552, 9))])
+# mirror of hs::ViewTexTable
+view_tex_dt = np.dtype([("tri_uv", "f4", (1552, 6)), ("sub_tex", "i4", (8, 3)), ("tex", "u8", 3)])

@@ -53,7 +53,7 @@ static isect isect_info(v3 d)
     return r;
 }
 
-static int tri_hit(const float *t, isect R, v3 org, float t_max, float *out_t)
+static int tri_hit(const float *t, isect R, v3 org, float t_max, float *out_t, float *bary)
 {
     v3 A = {t[0] - org.x, t[1] - org.y, t[2] - org.z};
     v3 B = {t[3] - org.x, t[4] - org.y, t[5] - org.z};
@@ -83,8 +83,42 @@ static int tri_hit(const float *t, isect R, v3 org, float t_max, float *out_t)
     float Az = R.Sz * a_kz, Bz = R.Sz * b_kz, Cz = R.Sz * c_kz;
     float T = fmaf(U, Az, fmaf(V, Bz, W * Cz));
     if (T < 0.f || T > t_max * det) return 0;
-    *out_t = T * (1.0f / det);
+    const float rcp = 1.0f / det;
+    *out_t = T * rcp;
+    bary[0] = U * rcp; bary[1] = V * rcp; bary[2] = W * rcp;
     return 1;
+}
+
+/* Optional texturing state (set once by the test): per-triangle texture coordinates, the
+ * texture index of each (object, submesh) material (-1 none) and up to 3 RGBA8 images.
+ * Sampling restates what `tex2D<float4>` does for the reference's texture objects
+ * (M/src/render/asset_processor.cpp:312-349: wrap addressing, linear filter, normalised
+ * coordinates, normalised-float reads) per the CUDA programming guide's texture-fetching
+ * appendix: xB = frac(u) * W - 0.5, i = floor(xB), blend weight = frac(xB) held with 8
+ * fractional bits; material lookup as bvh_raycast.cpp:783-797. */
+static const float *g_tri_uv = 0;
+static const int *g_sub_tex = 0;
+static const uint8_t *g_tex[3] = {0, 0, 0};
+static int g_tex_w[3], g_tex_h[3];
+
+void hs_oracle_set_uv(const float *tri_uv, const int *sub_tex) { g_tri_uv = tri_uv; g_sub_tex = sub_tex; }
+void hs_oracle_set_texture(int idx, const uint8_t *rgba, int w, int h) { g_tex[idx] = rgba; g_tex_w[idx] = w; g_tex_h[idx] = h; }
+
+static int wrapi(int i, int n) { i %= n; return i < 0 ? i + n : i; }
+
+static void sample_tex(int idx, float u, float v, float out[3])
+{
+    const int W = g_tex_w[idx], H = g_tex_h[idx];
+    float fu = u - floorf(u), fv = v - floorf(v);
+    float xb = fu * (float)W - 0.5f, yb = fv * (float)H - 0.5f;
+    float xf = floorf(xb), yf = floorf(yb);
+    float a = floorf((xb - xf) * 256.f + 0.5f) / 256.f, b = floorf((yb - yf) * 256.f + 0.5f) / 256.f;
+    int i0 = wrapi((int)xf, W), i1 = wrapi((int)xf + 1, W), j0 = wrapi((int)yf, H), j1 = wrapi((int)yf + 1, H);
+    for (int k = 0; k < 3; k++) {
+        float t00 = g_tex[idx][((size_t)j0 * W + i0) * 4 + k] / 255.f, t10 = g_tex[idx][((size_t)j0 * W + i1) * 4 + k] / 255.f;
+        float t01 = g_tex[idx][((size_t)j1 * W + i0) * 4 + k] / 255.f, t11 = g_tex[idx][((size_t)j1 * W + i1) * 4 + k] / 255.f;
+        out[k] = (1 - a) * (1 - b) * t00 + a * (1 - b) * t10 + (1 - a) * b * t01 + a * b * t11;
+    }
 }
 
 /* Renders one view.  Triangles are given per object id: object o owns triangles
@@ -119,7 +153,8 @@ int hs_oracle_render_view(const float *tris, const int *tri_sub, const int *obj_
             float pv = ((float)py + 0.5f) / (float)height;
             v3 d = nrm(sub(add(add(ll, scl(horizontal, pu)), scl(vertical, pv)), start));
             float t_max = 10000.f;
-            int hit = 0, hit_obj = 0, hit_sub = 0;
+            int hit = 0, hit_obj = 0, hit_sub = 0, hit_tri = 0;
+            float hit_bary[3] = {0, 0, 0};
             for (int i = 0; i < num_inst; i++) {
                 int o = inst_obj[i];
                 const float *s = inst_scale + 3 * i;
@@ -138,15 +173,28 @@ int hs_oracle_render_view(const float *tris, const int *tri_sub, const int *obj_
                 int any = 0;
                 for (int t = 0; t < obj_num_tri[o]; t++) {
                     int ti = obj_first_tri[o] + t;
-                    float th;
-                    if (tri_hit(tris + 9 * ti, R, ro, tm, &th)) { tm = th; any = 1; hit_sub = tri_sub[ti]; }
+                    float th, bc[3];
+                    if (tri_hit(tris + 9 * ti, R, ro, tm, &th, bc)) {
+                        tm = th; any = 1; hit_sub = tri_sub[ti]; hit_tri = ti;
+                        hit_bary[0] = bc[0]; hit_bary[1] = bc[1]; hit_bary[2] = bc[2];
+                    }
                 }
                 if (any) { t_max = tm / t_scale; hit = 1; hit_obj = o; }
             }
             size_t pix = (size_t)py * width + px;
             uint8_t *rgb = rgb_out + 4 * pix;
             if (hit) {
-                const float *c = sub_color + (hit_obj * 3 + hit_sub) * 3;
+                const float *mc = sub_color + (hit_obj * 3 + hit_sub) * 3;
+                float c[3] = {mc[0], mc[1], mc[2]};
+                int tex = g_sub_tex ? g_sub_tex[hit_obj * 3 + hit_sub] : -1;
+                if (tex >= 0 && g_tex[tex] && g_tri_uv) {
+                    const float *uv = g_tri_uv + 6 * hit_tri;
+                    float tu = uv[0] * hit_bary[0] + uv[2] * hit_bary[1] + uv[4] * hit_bary[2];
+                    float tv = uv[1] * hit_bary[0] + uv[3] * hit_bary[1] + uv[5] * hit_bary[2];
+                    float tc[3];
+                    sample_tex(tex, tu, 1.f - tv, tc);
+                    for (int k = 0; k < 3; k++) c[k] *= tc[k];
+                }
                 depth_out[pix] = t_max;
                 for (int k = 0; k < 3; k++) rgb[k] = (uint8_t)(fminf(1.f, fmaxf(0.2f, 0.f) * c[k]) * 255);
             } else {

@@ -24,7 +24,7 @@ def make(N, data_dir=None, size=64, **kw):
     sim = gh.HideAndSeekSimulator(num_worlds=N, enable_batch_renderer=True, batch_render_width=size,
                                   batch_render_height=size, render_data_dir=data_dir, **kw)
     sim.init()
-    return sim, gh.view_mesh_table(data_dir)
+    return sim, gh.view_mesh_table(data_dir), (gh.view_tex_table(data_dir) if data_dir else None)
 
 
 def drive(sim, steps, seed=0, A=4):
@@ -37,9 +37,10 @@ def drive(sim, steps, seed=0, A=4):
         sim.step()
 
 
-def check_views(sim, table, worlds, A, size=64, height=None):
+def check_views(sim, table, worlds, A, size=64, height=None, tex_table=None, data_dir=None):
     height = height or size
-    meshes = vu.Meshes(table)
+    meshes = vu.Meshes(table, tex_table, data_dir)
+    rgb_tol = 2 if tex_table is not None else 0       # textured materials go through the texture unit's filter
     depth = sim.depth_tensor().to_torch().cpu().numpy()
     rgb = sim.rgb_tensor().to_torch().cpu().numpy()
     assert depth.shape == (sim.num_worlds * A, height, size, 1) and depth.dtype == np.float32
@@ -49,7 +50,7 @@ def check_views(sim, table, worlds, A, size=64, height=None):
         dump = sim.dump_world(w)
         for k in range(A):
             rd, rc = vu.render_world_view(meshes, dump, k, size, height)
-            ok, frac, d = vu.compare(depth[w * A + k, :, :, 0], rgb[w * A + k], rd, rc, DEPTH_TOL, FLIP_FRAC)
+            ok, frac, d = vu.compare(depth[w * A + k, :, :, 0], rgb[w * A + k], rd, rc, DEPTH_TOL, FLIP_FRAC, rgb_tol)
             assert ok, (w, k, frac, d)
             worst, maxd = max(worst, frac), max(maxd, d)
             if dump["iface_slot"][k] >= 0:
@@ -66,10 +67,14 @@ def test_views_match_oracle(data_dir):
             pytest.skip("reference render meshes not present")
         data_dir = vu.REF_DATA
     N, A = 48, 4
-    sim, table = make(N, data_dir)
-    check_views(sim, table, range(0, N, 12), A)           # right after init
+    sim, table, tex = make(N, data_dir)
+    check_views(sim, table, range(0, N, 12), A, tex_table=tex, data_dir=data_dir)           # right after init
     drive(sim, 12)
-    worst, maxd = check_views(sim, table, range(0, N, 6), A)
+    worst, maxd = check_views(sim, table, range(0, N, 6), A, tex_table=tex, data_dir=data_dir)
+    if tex is not None:
+        # the textures do show: the ground is no longer one flat colour
+        rgb = sim.rgb_tensor().to_torch()[:, 40:, :, :3].reshape(-1, 3)
+        assert len(torch.unique(rgb, dim=0)) > 20
     print(f"views vs oracle: worst flipped-pixel fraction {worst:.2e}, max |depth diff| {maxd:.2e}")
 
 

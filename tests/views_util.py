@@ -30,14 +30,21 @@ def lib():
         _lib = C.CDLL(LIB_PATH)
         _lib.hs_oracle_render_view.argtypes = [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 6 + \
             [C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        _lib.hs_oracle_set_uv.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.hs_oracle_set_texture.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int]
     return _lib
 
 
-class Meshes:
-    """Per-object flat triangle lists out of a ViewMeshTable record."""
+TEXTURE_FILES = ["green_grid.png", "smile.png", "red_smile.png"]      # src/mgr.cpp:651-658
 
-    def __init__(self, table):
+
+class Meshes:
+    """Per-object flat triangle lists out of a ViewMeshTable record (+ texture coordinates and
+    images when the ViewTexTable of a data directory is given)."""
+
+    def __init__(self, table, tex_table=None, data_dir=None):
         tris, sub_of, first, num = [], [], np.zeros(8, np.int32), np.zeros(8, np.int32)
+        uvs = []
         for o in range(8):
             first[o] = len(tris)
             for s in range(int(table["obj_num_sub"][o])):
@@ -47,11 +54,31 @@ class Meshes:
                     for t in range(int(cb["count"])):
                         tris.append(table["tri"][int(cb["first"]) + t])
                         sub_of.append(s)
+                        if tex_table is not None:
+                            uvs.append(tex_table["tri_uv"][int(cb["first"]) + t])
             num[o] = len(tris) - first[o]
         self.tris = np.ascontiguousarray(np.array(tris, dtype=np.float32).reshape(-1, 9))
         self.tri_sub = np.array(sub_of, dtype=np.int32)
         self.first, self.num = first, num
         self.color = np.ascontiguousarray(table["sub_color"], dtype=np.float32)
+        self.uv = self.sub_tex = None
+        self.images = []
+        if tex_table is not None:
+            from PIL import Image
+            self.uv = np.ascontiguousarray(np.array(uvs, dtype=np.float32).reshape(-1, 6))
+            self.sub_tex = np.ascontiguousarray(tex_table["sub_tex"], dtype=np.int32)
+            for f in TEXTURE_FILES:
+                self.images.append(np.ascontiguousarray(np.array(Image.open(os.path.join(data_dir, f)).convert("RGBA"), dtype=np.uint8)))
+
+    def bind(self):
+        """Point the oracle's texturing state at this mesh set (or clear it)."""
+        l = lib()
+        if self.uv is None:
+            l.hs_oracle_set_uv(None, None)
+            return
+        l.hs_oracle_set_uv(self.uv.ctypes.data, self.sub_tex.ctypes.data)
+        for i, im in enumerate(self.images):
+            l.hs_oracle_set_texture(i, im.ctypes.data, im.shape[1], im.shape[0])
 
 
 def render(meshes, inst_obj, inst_pos, inst_rot, inst_scale, cam_pos, cam_rot, width=64, height=64, fov=100.0):
@@ -64,6 +91,7 @@ def render(meshes, inst_obj, inst_pos, inst_rot, inst_scale, cam_pos, cam_rot, w
     depth = np.zeros((height, width), dtype=np.float32)
     rgb = np.zeros((height, width, 4), dtype=np.uint8)
     p = lambda a: a.ctypes.data
+    meshes.bind()
     rc = lib().hs_oracle_render_view(p(meshes.tris), p(meshes.tri_sub), p(meshes.first), p(meshes.num),
                                      p(meshes.color), len(inst_obj), p(inst_obj), p(inst_pos), p(inst_rot),
                                      p(inst_scale), p(cam_pos), p(cam_rot), fov, width, height, p(depth), p(rgb))
@@ -81,11 +109,13 @@ def render_world_view(meshes, dump, iface, width=64, height=64):
     return render(meshes, b["obj"], b["pos"], b["rot"], b["scale"], b["pos"][slot], b["rot"][slot], width, height)
 
 
-def compare(depth, rgb, ref_depth, ref_rgb, tol=1e-4, max_flip_frac=2e-3):
-    """Depth within tol*max(1,depth) and identical colour, except for at most max_flip_frac of
-    the pixels (silhouette pixels where a 1-ulp difference flips hit/miss or the hit instance)."""
+def compare(depth, rgb, ref_depth, ref_rgb, tol=1e-4, max_flip_frac=2e-3, rgb_tol=0):
+    """Depth within tol*max(1,depth) and colour bytes within rgb_tol (0 without textures: the
+    hardware bilinear filter is only restated to its documented 8 fractional weight bits),
+    except for at most max_flip_frac of the pixels (silhouette pixels where a 1-ulp difference
+    flips hit/miss or the hit instance)."""
     d = np.abs(depth - ref_depth)
-    bad = (d > tol * np.maximum(1.0, np.abs(ref_depth))) | (rgb != ref_rgb).any(-1)
+    bad = (d > tol * np.maximum(1.0, np.abs(ref_depth))) | (np.abs(rgb.astype(np.int16) - ref_rgb.astype(np.int16)) > rgb_tol).any(-1)
     frac = bad.mean()
     ok = ~bad
     return frac <= max_flip_frac, frac, float(d[ok].max()) if ok.any() else 0.0
