@@ -140,6 +140,8 @@ int hs_view_mesh_table_bytes(void);
 int hs_build_view_mesh_table(const char *data_dir, void *out, int out_bytes);
 int hs_view_tex_table_bytes(void);       /* hs::ViewTexTable: per-triangle UVs, material -> texture */
 int hs_build_view_tex_table(const char *data_dir, void *out, int out_bytes);
+/* host only: the PNG reader used for the view textures (8-bit RGB / RGBA, non-interlaced) */
+int hs_decode_png(const char *path, int *width, int *height, uint8_t *out, int64_t cap);
 
 /* Diagnostics / parity: flat per-world internal state (layout in
  * hideseek/debug_dump.h), number of kernels launched by the last hs_step,

@@ -568,6 +568,18 @@ extern "C" int hs_build_view_mesh_table(const char *data_dir, void *out, int out
     return 0;
 }
 
+// host-only diagnostic: the PNG reader hs_enable_views uses for the textures.  `out` receives
+// width*height RGBA8 pixels if it has room (`cap` bytes); width / height are always reported.
+extern "C" int hs_decode_png(const char *path, int *width, int *height, uint8_t *out, int64_t cap)
+{
+    if (!path || !width || !height) { g_err = "hs_decode_png: null argument"; return 1; }
+    std::vector<uint8_t> rgba;
+    const char *err = decodePngRGBA(path, width, height, rgba);
+    if (err[0]) { g_err = std::string("hs_decode_png: ") + err; return 1; }
+    if (out && cap >= (int64_t)rgba.size()) memcpy(out, rgba.data(), rgba.size());
+    return 0;
+}
+
 extern "C" int hs_view_tex_table_bytes(void) { return (int)sizeof(ViewTexTable); }
 
 // host-only: per-triangle texture coordinates and material -> texture bindings for `data_dir`

@@ -120,3 +120,44 @@ def test_table_capacity_and_clusters():
                 tri = t["tri"][int(cb["first"]):int(cb["first"]) + int(cb["count"])].reshape(-1, 3)
                 assert (tri >= cb["lo"]).all() and (tri <= cb["hi"]).all()
                 assert (cb["lo"] >= sb["lo"] - 1e-4).all() and (cb["hi"] <= sb["hi"] + 1e-4).all()
+
+
+@pytest.mark.skipif(not vu.have_ref_data(), reason="reference textures not present")
+def test_png_reader_matches_pil():
+    import ctypes as C
+    import os
+    import gpu_hideseek as gh
+    from PIL import Image
+    lib = gh.load_library()
+    lib.hs_decode_png.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p, C.c_int64]
+    for name in vu.TEXTURE_FILES:
+        path = os.path.join(vu.REF_DATA, name)
+        want = np.array(Image.open(path).convert("RGBA"), dtype=np.uint8)
+        w, h = C.c_int(), C.c_int()
+        assert lib.hs_decode_png(path.encode(), C.byref(w), C.byref(h), None, 0) == 0
+        assert (h.value, w.value) == want.shape[:2]
+        got = np.zeros_like(want)
+        assert lib.hs_decode_png(path.encode(), C.byref(w), C.byref(h), got.ctypes.data, got.nbytes) == 0
+        assert np.array_equal(got, want), name
+    w, h = C.c_int(), C.c_int()
+    assert lib.hs_decode_png(b"/nonexistent.png", C.byref(w), C.byref(h), None, 0) != 0
+    assert lib.hs_decode_png(os.path.join(vu.REF_DATA, "plane.obj").encode(), C.byref(w), C.byref(h), None, 0) != 0
+
+
+@pytest.mark.skipif(not vu.have_ref_data(), reason="reference render meshes not present")
+def test_texture_coordinates_and_bindings():
+    import gpu_hideseek as gh
+    X, T = gh.view_tex_table(vu.REF_DATA), gh.view_mesh_table(vu.REF_DATA)
+    assert X["sub_tex"][OBJ_PLANE][0] == 0 and X["sub_tex"][OBJ_HIDER][0] == 1 and X["sub_tex"][OBJ_SEEKER][0] == 2
+    assert (X["sub_tex"][[OBJ_CUBE, OBJ_WALL, OBJ_RAMP, OBJ_BOX]] == -1).all() and (X["sub_tex"][:, 1:] == -1).all()
+    # the ground quad is tiled 200 x 200 (data/plane.obj), the agent meshes stay inside [0, 1]
+    ground = int(T["cluster"][int(T["sub"][int(T["obj_first_sub"][OBJ_PLANE])]["first"])]["first"])
+    assert set(np.unique(X["tri_uv"][ground:ground + 2])) == {0.0, 200.0}
+    uv = X["tri_uv"][:int(T["num_tris"])]
+    assert uv[int(T["num_small_tris"]):].min() >= 0.0 and uv[int(T["num_small_tris"]):].max() <= 1.0
+    # built-in meshes: no textures
+    assert (gh.view_tex_table()["sub_tex"] == -1).all()
+    # the oracle's textured ground shows the grid: many distinct colours instead of one
+    m = vu.Meshes(T, X, vu.REF_DATA)
+    _, rgb = vu.render(m, [OBJ_PLANE], [[0, 0, 0]], [ID], [[1, 1, 1]], [0.3, 0.2, 1.0], ID)
+    assert len(np.unique(rgb[40:].reshape(-1, 4), axis=0)) > 5
