@@ -34,9 +34,19 @@ constexpr int kViewMaxClusters = 200;
 constexpr int kViewMaxSubmeshes = 16;
 constexpr int kViewMaxSubPerObj = 3;
 constexpr int kViewClusterTris = 8;       // <= 64 clusters per submesh (one 64-bit mask)
-constexpr int kViewThreads = 256;
+#ifndef HS_VIEW_THREADS
+#define HS_VIEW_THREADS 256
+#endif
+#ifndef HS_VIEW_CTAS
+#define HS_VIEW_CTAS 3
+#endif
+#ifndef HS_VIEW_TILE_W
+#define HS_VIEW_TILE_W 8
+#endif
+constexpr int kViewThreads = HS_VIEW_THREADS;
+constexpr int kViewTileW = HS_VIEW_TILE_W, kViewTileH = 32 / HS_VIEW_TILE_W;   // a warp's pixel tile
 constexpr int kViewSmallTris = 16;     // a mesh of at most this many triangles is one flat list with a 16-bit facing mask
-constexpr int kViewCtasPerSm = 3;
+constexpr int kViewCtasPerSm = HS_VIEW_CTAS;
 
 struct ViewBox { float lo[3]; int first; float hi[3]; int count; };     // 32 B
 struct ViewMeshTable {
@@ -313,7 +323,7 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
     __syncthreads();
 
     const int lane = tid & 31;
-    const int tilesX = (W + 7) / 8, tilesY = (H + 3) / 4;
+    const int tilesX = (W + kViewTileW - 1) / kViewTileW, tilesY = (H + kViewTileH - 1) / kViewTileH;
     const Vec3 o = sm.origin;
     const Vec3 LL = sm.lowerLeft - o, HZ = sm.horizontal, VT = sm.vertical;
     for (;;) {
@@ -321,14 +331,14 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
         if (lane == 0) tile = atomicAdd(&sm.nextTile, 1);
         tile = __shfl_sync(0xffffffffu, tile, 0);
         if (tile >= tilesX * tilesY) break;
-        const int px0 = (tile % tilesX) * 8, py0 = (tile / tilesX) * 4;
+        const int px0 = (tile % tilesX) * kViewTileW, py0 = (tile / tilesX) * kViewTileH;
         // Warp-cooperative cull: lane j tests instances j and j+32 against the pyramid of this
         // 8x4-pixel tile (apex = camera, four side planes through the tile's corner rays); the
         // rays then only visit the instances some ray of the tile can reach, still front to back.
         uint64_t todo;
         {
-            const float u0 = float(px0) / float(W), u1 = float(min(px0 + 8, W)) / float(W);
-            const float v0 = float(py0) / float(H), v1 = float(min(py0 + 4, H)) / float(H);
+            const float u0 = float(px0) / float(W), u1 = float(min(px0 + kViewTileW, W)) / float(W);
+            const float v0 = float(py0) / float(H), v1 = float(min(py0 + kViewTileH, H)) / float(H);
             const Vec3 c00 = LL + u0 * HZ + v0 * VT, c10 = LL + u1 * HZ + v0 * VT;
             const Vec3 c01 = LL + u0 * HZ + v1 * VT, c11 = LL + u1 * HZ + v1 * VT;
             const Vec3 cen = c00 + c11;
@@ -353,7 +363,7 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
             }
             todo = uint64_t(__ballot_sync(0xffffffffu, keep[0])) | (uint64_t(__ballot_sync(0xffffffffu, keep[1])) << 32);
         }
-        const int px = px0 + (lane & 7), py = py0 + (lane >> 3);
+        const int px = px0 + (lane % kViewTileW), py = py0 + (lane / kViewTileW);
         if (px >= W || py >= H) continue;
         float pu = (float(px) + 0.5f) / float(W);
         float pv = (float(py) + 0.5f) / float(H);
