@@ -13,12 +13,14 @@
 //   * depth = distance along the unit ray to the closest hit, 0 on a miss; this environment
 //     creates no light entities, so computeFragment's colour is max(0.2, 0) * material colour
 //     (bvh_raycast.cpp:848-935); rgb bytes = colour * 255 truncated, alpha 255 (:822-839).
-// What differs by design: no TLAS/BLAS walk — a world has <= 52 instances, so a CTA stages
-// their object-space transforms and world AABBs in shared memory once per view, sorted front
-// to back, and every pixel runs one uniform loop over them (slab cull against the closest hit
-// so far, then the mesh's triangles).  Which triangles of a box / wedge / ground instance face
-// the camera is decided once per view, not per pixel.  This file is its own translation unit
-// (hs_views.cu) compiled with FMA contraction on: nothing here has to match a CPU bit for bit.
+// What differs by design: no TLAS/BLAS walk with a per-thread stack.  Persistent CTAs keep the
+// whole render-mesh table in shared memory; per view, the world's <= 52 instances are staged in
+// shared memory front to back with their object-space maps; which triangles (ground / boxes /
+// wedge) or triangle clusters (agents) face the camera is decided once per view, not per pixel;
+// a warp culls the instance list against its 8x4-pixel tile's pyramid cooperatively, and each
+// ray then walks the survivors (slab test against the closest hit so far, then triangles).
+// This file is its own translation unit (hs_views.cu) compiled with FMA contraction and fast
+// division: nothing here has to match a CPU bit for bit.
 // The three textures (ground grid, hider / seeker faces) are sampled through CUDA texture
 // objects set up like the reference's when a data directory is given; the built-in meshes have
 // no texture coordinates and use the material's base colour.  Inactive agent slots produce an
