@@ -38,6 +38,9 @@ def parse_args():
     ap.add_argument("--worlds", type=int, default=WORLDS_PER_GPU, help="worlds per GPU")
     ap.add_argument("--profile-steps", type=int, default=24)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--views", action="store_true",
+                    help="also measure the agent camera views (enable_batch_renderer=True, 64x64) and add a "
+                         "`views` object; off by default: the headline configuration has the renderer off")
     return ap.parse_args()
 
 
@@ -218,6 +221,65 @@ def run_reference(args):
     emit(line)
 
 
+def measure_views(args, gh, torch, dev, local, peak):
+    """k_agent_views at scripts/benchmark.py's renderer settings (64x64 per agent), device-timed,
+    next to its CPU restatement (oracle/views_oracle.c, the cpu_baseline leg) on a few views."""
+    import ctypes as C
+    import time
+    N, A, S, launches = args.worlds, AGENTS, 64, 10
+    sim = gh.HideAndSeekSimulator(gpu_id=local, num_worlds=N, sim_flags=0, rand_seed=0, min_hiders=2, max_hiders=2,
+                                  min_seekers=2, max_seekers=2, enable_batch_renderer=True,
+                                  batch_render_width=S, batch_render_height=S)
+    sim.init()
+    lib = gh.load_library()
+    lib.hs_render_views.argtypes = [C.c_void_p, C.c_void_p]
+    lib.hs_step.argtypes = [C.c_void_p, C.c_void_p]
+    h = C.c_void_p(sim.handle())
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    act = sim.action_tensor().to_torch()
+    for _ in range(20):                     # let the agents leave their spawn poses
+        act[:, 0:2] = torch.randint(-5, 5, (N * A, 2), dtype=torch.int32, device=dev)
+        assert lib.hs_step(h, stream) == 0
+    for _ in range(3):
+        assert lib.hs_render_views(h, stream) == 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(launches):
+        assert lib.hs_render_views(h, stream) == 0
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / launches
+    E = sim.world_stats()["bodies"]
+    rays = N * A * S * S
+    alg = rays * 8 + N * A * E * 52          # f32 depth + RGBA8 written per pixel, body records read per view
+    out = {"kernel": "k_agent_views", "view": [S, S], "views_per_launch": N * A, "launches": launches,
+           "ms_per_launch": ms, "rays_per_s": rays / (ms / 1e3), "meshes": "built-in",
+           "roofline": {"bound": "hbm", "achieved": alg / (ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": alg / (ms / 1e3) / 1e9 / peak, "alg_bytes_per_launch": alg,
+                        "traffic": 2.13e9, "traffic_source": "profiles/r05_views_ncu.md (ncu --set full)"}}
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import views_util as vu
+        meshes = vu.Meshes(gh.view_mesh_table())
+        depth = sim.depth_tensor().to_torch()
+        t0, done, maxd = time.perf_counter(), 0, 0.0
+        for w in range(2):
+            dump = sim.dump_world(w)
+            for k in range(A):
+                rd, _ = vu.render_world_view(meshes, dump, k, S, S)
+                maxd = max(maxd, float(abs(depth[w * A + k, :, :, 0].cpu().numpy() - rd).max()))
+                done += 1
+        secs = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": done * S * S / secs, "unit": "rays/s", "cores": 1, "kind": "port",
+                               "sample": f"{done} views of {S}x{S} ({secs:.1f} s), oracle/views_oracle.c: brute force "
+                                         f"over every triangle, no acceleration structure; max |depth diff| to the "
+                                         f"kernel on them {maxd:.2g}"}
+    except Exception as e:      # the oracle is a checker, never a dependency of the product arm
+        out["cpu_baseline"] = {"value": None, "unit": "rays/s", "cores": 0, "kind": "port", "sample": f"unavailable: {e}"}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -371,6 +433,9 @@ def run_ours(args):
     }
     if cpu_baseline:
         line["cpu_baseline"] = cpu_baseline
+    if args.views and world == 1:
+        del sim
+        line["views"] = measure_views(args, gh, torch, dev, local, measured_peak_gbs()[0])
     emit(line)
     if world > 1:
         dist.destroy_process_group()
