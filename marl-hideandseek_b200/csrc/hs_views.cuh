@@ -328,6 +328,7 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
     const int tilesX = (W + kViewTileW - 1) / kViewTileW, tilesY = (H + kViewTileH - 1) / kViewTileH;
     const Vec3 o = sm.origin;
     const Vec3 LL = sm.lowerLeft - o, HZ = sm.horizontal, VT = sm.vertical;
+    const float sU = dot(cross(LL, VT), HZ) < 0.f ? -1.f : 1.f, sV = dot(cross(LL, HZ), VT) < 0.f ? -1.f : 1.f;
     for (;;) {
         int tile = 0;
         if (lane == 0) tile = atomicAdd(&sm.nextTile, 1);
@@ -341,14 +342,11 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
         {
             const float u0 = float(px0) / float(W), u1 = float(min(px0 + kViewTileW, W)) / float(W);
             const float v0 = float(py0) / float(H), v1 = float(min(py0 + kViewTileH, H)) / float(H);
-            const Vec3 c00 = LL + u0 * HZ + v0 * VT, c10 = LL + u1 * HZ + v0 * VT;
-            const Vec3 c01 = LL + u0 * HZ + v1 * VT, c11 = LL + u1 * HZ + v1 * VT;
-            const Vec3 cen = c00 + c11;
-            Vec3 nl = cross(c00, c01), nr = cross(c10, c11), nt = cross(c00, c10), nb = cross(c01, c11);
-            if (dot(nl, cen) < 0.f) nl = -nl;
-            if (dot(nr, cen) < 0.f) nr = -nr;
-            if (dot(nt, cen) < 0.f) nt = -nt;
-            if (dot(nb, cen) < 0.f) nb = -nb;
+            // side planes of the pyramid, normals pointing inward.  All directions of one pixel
+            // column LL + u*HZ + v*VT (u fixed) lie in the plane with normal (LL + u*HZ) x VT, so
+            // a plane needs one cross product; which way is "inward" is the same for every tile.
+            const Vec3 nl = sU * cross(LL + u0 * HZ, VT), nr = -sU * cross(LL + u1 * HZ, VT);
+            const Vec3 nt = sV * cross(LL + v0 * VT, HZ), nb = -sV * cross(LL + v1 * VT, HZ);
             bool keep[2];
 #pragma unroll
             for (int r = 0; r < 2; r++) {
