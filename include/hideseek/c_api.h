@@ -148,6 +148,12 @@ int hs_decode_png(const char *path, int *width, int *height, uint8_t *out, int64
  * capacity-overflow counter. */
 int hs_dump_world(hs_sim *sim, int world, void *out, int out_bytes);
 int hs_world_dump_bytes(void);
+/* Bulk parity dump: `count` hs_compact_world records (debug_dump.h) of worlds [world0, world0 +
+ * count) into host memory.  hs_set_debug(flags): bit 0 makes the ray stage record which body
+ * every lidar ray hit (reported in the compact record); takes effect from the next hs_step. */
+int hs_compact_dump_bytes(void);
+int hs_dump_compact(hs_sim *sim, int world0, int count, void *out, int64_t out_bytes);
+int hs_set_debug(hs_sim *sim, unsigned flags);
 int hs_last_step_launches(hs_sim *sim);
 int hs_overflow_count(hs_sim *sim, uint32_t *out);
 

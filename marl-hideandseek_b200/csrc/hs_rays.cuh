@@ -416,6 +416,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
         if (!active) continue;
         if (isLidar) {
             S.exLidar[(size_t(w) * A + k) * 30 + (r - k * 30)] = hit < 0 ? 0.f : t;
+            if (S.p.debugFlags & 1u) S.dbgLidarHit[(size_t(w) * A + k) * 30 + (r - k * 30)] = int8_t(hit);
         } else {
             const int info = sm.visInfo[q];
             const bool vis = hit == ((info >> 3) & 0xFF);

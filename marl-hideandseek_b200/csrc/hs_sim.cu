@@ -87,6 +87,8 @@ static int devAlloc(hs_sim *sim, T **out, size_t count)
 
 extern "C" const char *hs_last_error(void) { return g_err.c_str(); }
 
+static int createBody(hs_sim *sim, const hs_config *cfg, int A);
+
 extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
 {
     if (!cfg || !out) { g_err = "hs_create: null argument"; return 1; }
@@ -105,6 +107,16 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
 
     hs_sim *sim = new hs_sim();
     sim->cfg = *cfg;
+    if (createBody(sim, cfg, A) != 0) {      // g_err is set; release whatever was allocated so far
+        hs_destroy(sim);
+        return 1;
+    }
+    *out = sim;
+    return 0;
+}
+
+static int createBody(hs_sim *sim, const hs_config *cfg, int A)
+{
     DeviceState &S = sim->S;
     const size_t N = (size_t)cfg->num_worlds;
     RandKey ik = initKey(cfg->rand_seed);
@@ -125,6 +137,7 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
     HS_TRY(devAlloc(sim, &S.contact, size_t(kMaxCand) * kContactWords * N));
     HS_TRY(devAlloc(sim, &S.cmeta, size_t(kMaxCand) * N));
     HS_TRY(devAlloc(sim, &S.overflow, 4));
+    HS_TRY(devAlloc(sim, &S.dbgLidarHit, N * A * 30));
 
     const size_t R = N * A;
     HS_TRY(devAlloc(sim, &S.exReset, N));
@@ -203,7 +216,6 @@ extern "C" int hs_create(const hs_config *cfg, hs_sim **out)
         float ang = mult * (135.f / 2.f);
         sim->cosThreshold = (float)cos((double)ang);
     }
-    *out = sim;
     return 0;
 }
 
@@ -322,6 +334,119 @@ __global__ void k_dump_world(DeviceState S, int w, hs_world_dump *out)
     }
 }
 
+
+// ---- bulk parity dump (hs_compact_world, include/hideseek/debug_dump.h) ---------------------------
+// One CTA per world; every section is a lane-strided copy.
+__global__ void k_dump_compact(DeviceState S, int w0, hs_compact_world *out)
+{
+    const int w = w0 + blockIdx.x, t = threadIdx.x, T = blockDim.x;
+    hs_compact_world &d = out[blockIdx.x];
+    const int nb = WI(S, WF_NUM_BODIES, w), nDyn = WI(S, WF_NUM_DYN, w), A = S.p.agentsPerWorld;
+    if (t == 0) {
+        d.cur_episode_step = WI(S, WF_EPISODE_STEP, w);
+        d.cur_world_episode = WI(S, WF_WORLD_EPISODE, w);
+        d.rng_key[0] = WI(S, WF_RNG_A, w); d.rng_key[1] = WI(S, WF_RNG_B, w);
+        d.rng_count = WI(S, WF_RNG_COUNT, w);
+        d.num_hiders = WI(S, WF_NUM_HIDERS, w); d.num_seekers = WI(S, WF_NUM_SEEKERS, w);
+        d.num_boxes = WI(S, WF_NUM_BOXES, w); d.num_ramps = WI(S, WF_NUM_RAMPS, w);
+        d.hider_team_reward = __int_as_float(WI(S, WF_HIDER_REWARD, w));
+        d.seekers_first = WI(S, WF_SEEKERS_FIRST, w);
+        d.running_scores[0] = WI(S, WF_SCORE0, w); d.running_scores[1] = WI(S, WF_SCORE1, w);
+        d.num_bodies = nb; d.num_dyn = nDyn;
+        const uint32_t *blob = BVH(S, w);
+        d.bvh_num_nodes = blob[0]; d.bvh_num_leaves = blob[1];
+        // candidates in emission order; contacts of the last substep in creation order
+        const int nc = WI(S, WF_NUM_CAND, w);
+        d.num_cand = nc;
+        int K = 0;
+        for (int c = 0; c < nc; c++) {
+            const uint32_t m = S.cmeta[size_t(w) * kMaxCand + c];
+            if ((m >> 16) == 0) continue;
+            if (K < HS_COMPACT_MAX_CONTACTS) {
+                d.contact_ref[K] = m & 0xFF; d.contact_alt[K] = (m >> 8) & 0xFF; d.contact_npts[K] = (m >> 16) & 0xFF;
+                const float *row = S.contact + (size_t(w) * kMaxCand + c) * kContactWords;
+                for (int p = 0; p < 4; p++) for (int k = 0; k < 4; k++) d.contact_pts[K][p][k] = row[p * 4 + k];
+                for (int k = 0; k < 3; k++) d.contact_normal[K][k] = row[16 + k];
+                d.contact_lambda[K] = row[19];
+            }
+            K++;
+        }
+        d.num_contacts = K;
+        for (int k = 0; k < HS_DUMP_MAX_AGENTS; k++) {
+            const uint32_t jm = k < nb - nDyn ? JMETA(S, k, w) : 0xFFFFFFFFu;
+            d.joint_other[k] = jm == 0xFFFFFFFFu ? -1 : int8_t(jm & 0xFF);
+            d.joint_sep[k] = jm == 0xFFFFFFFFu ? 0.f : JF(S, JF_SEP, k, w);
+        }
+    }
+    for (int s = t; s < HS_DUMP_MAX_BODIES; s += T) {
+        const bool live = s < nb;
+        const uint32_t m = live ? META(S, s, w) : 0u;
+        d.obj[s] = live ? metaObj(m) : 0; d.response[s] = live ? metaResp(m) : 0;
+        d.owner[s] = live ? metaOwner(m) : 0; d.leaf[s] = live ? metaLeaf(m) : 0;
+        int rank = 0;
+        for (int o = 0; live && o < nb; o++) rank += metaEid(META(S, o, w)) < metaEid(m);
+        d.eid_rank[s] = uint8_t(rank);
+        for (int k = 0; k < 7; k++) d.pose[s][k] = live ? BF(S, BF_PX + k, s, w) : 0.f;
+        for (int k = 0; k < 3; k++) d.scale[s][k] = live ? BF(S, BF_SX + k, s, w) : 0.f;
+        for (int k = 0; k < 6; k++) d.vel[s][k] = live ? BF(S, BF_VX + k, s, w) : 0.f;
+        for (int k = 0; k < 6; k++) d.force[s][k] = live ? BF(S, BF_FX + k, s, w) : 0.f;
+    }
+    const uint32_t *blob = BVH(S, w);
+    for (int i = t; i < kMaxNodes * 24; i += T) d.node_bounds[i / 24][i % 24] = nodeF(blob, i / 24)[i % 24];
+    for (int i = t; i < kMaxNodes * 4; i += T) d.node_children[i / 4][i % 4] = nodeI(blob, i / 4)[kNodeChild + i % 4];
+    for (int i = t; i < kMaxNodes; i += T) d.node_parent[i] = nodeI(blob, i)[kNodeParent];
+    for (int i = t; i < kMaxBodies * 6; i += T) d.leaf_aabb[i / 6][i % 6] = leafF(blob, i / 6)[i % 6];
+    for (int i = t; i < kMaxBodies; i += T) d.leaf_parent[i] = blob[kBvhLeafOff + i * kLeafWords + kLeafParent];
+    for (int c = t; c < kMaxCand; c += T) {
+        const uint16_t v = S.cand[size_t(w) * kMaxCand + c];
+        d.cand[c][0] = v & 0xFF; d.cand[c][1] = v >> 8;
+    }
+    for (int i = t; i < HS_DUMP_MAX_AGENTS * 30; i += T) {
+        const int k = i / 30;
+        int8_t v = -2;
+        if (k < A && WB(S, WB_IFACE_SLOT + k, w) != 0xFF) v = S.dbgLidarHit[(size_t(w) * A + k) * 30 + i % 30];
+        d.lidar_hit[k][i % 30] = v;
+    }
+}
+
+extern "C" int hs_compact_dump_bytes(void) { return (int)sizeof(hs_compact_world); }
+
+extern "C" int hs_dump_compact(hs_sim *sim, int world0, int count, void *out, int64_t out_bytes)
+{
+    if (!sim || !out || world0 < 0 || count <= 0 || world0 + count > sim->cfg.num_worlds ||
+        out_bytes < (int64_t)count * (int64_t)sizeof(hs_compact_world)) {
+        g_err = "hs_dump_compact: bad argument";
+        return 1;
+    }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    HS_CUDA(cudaDeviceSynchronize());
+    hs_compact_world *dev = nullptr;
+    const size_t bytes = size_t(count) * sizeof(hs_compact_world);
+    HS_CUDA(cudaMalloc(&dev, bytes));
+    cudaError_t e = cudaMemset(dev, 0, bytes);
+    if (e == cudaSuccess) {
+        k_dump_compact<<<count, 64>>>(sim->S, world0, dev);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(out, dev, bytes, cudaMemcpyDeviceToHost);
+    cudaFree(dev);
+    HS_CUDA(e);
+    return 0;
+}
+
+extern "C" int hs_set_debug(hs_sim *sim, unsigned flags)
+{
+    if (!sim) { g_err = "hs_set_debug: null sim"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
+    HS_CUDA(cudaDeviceSynchronize());
+    sim->S.p.debugFlags = flags;
+    if (sim->stepGraph) {                   // kernel arguments are baked into the graph: recapture
+        cudaGraphExecDestroy(sim->stepGraph);
+        sim->stepGraph = nullptr;
+    }
+    return 0;
+}
+
 extern "C" int hs_world_dump_bytes(void) { return (int)sizeof(hs_world_dump); }
 
 extern "C" int hs_dump_world(hs_sim *sim, int world, void *out, int out_bytes)
@@ -340,11 +465,13 @@ extern "C" int hs_dump_world(hs_sim *sim, int world, void *out, int out_bytes)
 
 extern "C" int hs_overflow_count(hs_sim *sim, uint32_t *out)
 {
+    if (!sim || !out) { g_err = "hs_overflow_count: null argument"; return 1; }
+    HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
     HS_CUDA(cudaMemcpy(out, sim->S.overflow, 4, cudaMemcpyDeviceToHost));
     return 0;
 }
 
-extern "C" int hs_last_step_launches(hs_sim *sim) { return sim->lastLaunches; }
+extern "C" int hs_last_step_launches(hs_sim *sim) { return sim ? sim->lastLaunches : 0; }
 
 // ---- launch sequence ------------------------------------------------------------
 namespace {
@@ -597,6 +724,7 @@ extern "C" int hs_build_view_tex_table(const char *data_dir, void *out, int out_
 
 extern "C" int hs_sync(hs_sim *sim, void *stream)
 {
+    if (!sim) { g_err = "hs_sync: null sim"; return 1; }
     HS_CUDA(cudaSetDevice(sim->cfg.gpu_id));
     HS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return 0;

@@ -179,6 +179,7 @@ struct SimParams {
     uint32_t simFlags;
     uint32_t initKeyA, initKeyB;     // rand::initKey(seed)
     int minHiders, maxHiders, minSeekers, maxSeekers;
+    uint32_t debugFlags;             // hs_set_debug: bit 0 = record lidar hit bodies
 };
 
 struct DeviceState {
@@ -197,6 +198,7 @@ struct DeviceState {
     float *contact;          // [N][kMaxCand][kContactWords]
     uint32_t *cmeta;         // [N][kMaxCand]
     uint32_t *overflow;      // [1] candidate-capacity overflow counter
+    int8_t *dbgLidarHit;     // [N*A][30] body slot every lidar ray hit (debugFlags bit 0), -1 miss
 
     // exported tensors (reference ExportID order, src/sim.hpp:45-68)
     int32_t *exReset;        // [N,1]
@@ -238,6 +240,7 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
     V.cand += b * kMaxCand;
     V.contact += b * kMaxCand * kContactWords;
     V.cmeta += b * kMaxCand;
+    V.dbgLidarHit += b * A * 30;
     V.exReset += b; V.exPrepCounter += b * A; V.exAction += b * A * 5; V.exSelfObs += b * A * 13;
     V.exSelfType += b * A; V.exSelfMask += b * A; V.exAgentObs += b * A * 5 * 14;
     V.exBoxObs += b * A * 9 * 17; V.exRampObs += b * A * 2 * 14; V.exAgentVis += b * A * 5;

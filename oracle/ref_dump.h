@@ -103,4 +103,46 @@ typedef struct {
     uint32_t hedges[HSREF_MAX_HULL_HEDGES][3];   /* next, rootVertex, face */
 } hsref_object;
 
+/* Compact per-world record for bulk parity runs: the same layout as hs_compact_world
+ * (include/hideseek/debug_dump.h), restated here so that nothing under oracle/ depends on the
+ * product tree; tests/compact.py asserts the two sizes agree.  Body arrays are indexed by ECS
+ * iteration order.  cand / contact_* / lidar_hit are filled by hsref_step_probe. */
+#define HSREF_C_BODIES 52
+#define HSREF_C_NODES 69
+#define HSREF_C_CAND 256
+#define HSREF_C_CONTACTS 96
+
+typedef struct {
+    int32_t cur_episode_step, cur_world_episode;
+    uint32_t rng_key[2];
+    uint32_t rng_count;
+    int32_t num_hiders, num_seekers, num_boxes, num_ramps;
+    float hider_team_reward;
+    int32_t seekers_first;
+    int32_t running_scores[2];
+    int32_t num_bodies, num_dyn;
+    int32_t bvh_num_leaves, bvh_num_nodes;
+    int32_t num_cand, num_contacts;
+    uint8_t obj[HSREF_C_BODIES], response[HSREF_C_BODIES], owner[HSREF_C_BODIES], leaf[HSREF_C_BODIES];
+    uint8_t eid_rank[HSREF_C_BODIES];
+    int8_t joint_other[HSREF_MAX_AGENTS];
+    int8_t pad0[2];
+    float joint_sep[HSREF_MAX_AGENTS];
+    float pose[HSREF_C_BODIES][7];
+    float scale[HSREF_C_BODIES][3];
+    float vel[HSREF_C_BODIES][6];
+    float force[HSREF_C_BODIES][6];
+    float node_bounds[HSREF_C_NODES][24];
+    int32_t node_children[HSREF_C_NODES][4];
+    int32_t node_parent[HSREF_C_NODES];
+    float leaf_aabb[HSREF_C_BODIES][6];
+    uint32_t leaf_parent[HSREF_C_BODIES];
+    uint8_t cand[HSREF_C_CAND][2];
+    uint8_t contact_ref[HSREF_C_CONTACTS], contact_alt[HSREF_C_CONTACTS], contact_npts[HSREF_C_CONTACTS];
+    float contact_pts[HSREF_C_CONTACTS][4][4];
+    float contact_normal[HSREF_C_CONTACTS][3];
+    float contact_lambda[HSREF_C_CONTACTS];
+    int8_t lidar_hit[HSREF_MAX_AGENTS][30];
+} hsref_compact;
+
 #endif

@@ -39,16 +39,39 @@
 
 #include "ref_dump.h"
 
+// The contact solver state lives in an archetype column whose component type is private to
+// M/src/physics/xpbd.cpp:9-11; component ids are tracked by type NAME, so declaring the same
+// one-member struct under the same name lets the probe read the stored normal multiplier.
+namespace madrona::phys::xpbd {
+struct XPBDContactState {
+    float lambdaN[4];
+};
+}
+
 using namespace GPUHideSeek;
 namespace bp = madrona::phys::broadphase;
 
 namespace {
+
+// what hsref_step_probe captures per world (the part of hsref_compact no export shows)
+struct ProbeData {
+    int32_t numCand, numContacts;
+    uint8_t cand[HSREF_C_CAND][2];
+    uint8_t ref[HSREF_C_CONTACTS], alt[HSREF_C_CONTACTS], npts[HSREF_C_CONTACTS];
+    float pts[HSREF_C_CONTACTS][4][4];
+    float normal[HSREF_C_CONTACTS][3];
+    float lambda[HSREF_C_CONTACTS];
+    int8_t lidarHit[HSREF_MAX_AGENTS][30];
+};
 
 struct Handle {
     Manager *mgr;
     Manager::CPUImpl *impl;
     int numWorlds;
     int agentsPerWorld;
+    std::vector<ProbeData> probe;       // empty until the first hsref_step_probe
+    int candClearNode = -1;             // Step-graph node that clears the candidate pairs
+    int contactClearNode = -1;          // ... the contacts of the LAST substep
 };
 
 inline Manager::CPUImpl *cpuImpl(Manager *m)
@@ -97,9 +120,11 @@ void *hsref_create(int num_worlds, uint32_t sim_flags, uint32_t seed,
 
     pthread_setaffinity_np(pthread_self(), sizeof(orig), &orig);
 
-    Handle *h = new Handle {
-        mgr, cpuImpl(mgr), num_worlds, max_hiders + max_seekers,
-    };
+    Handle *h = new Handle();
+    h->mgr = mgr;
+    h->impl = cpuImpl(mgr);
+    h->numWorlds = num_worlds;
+    h->agentsPerWorld = max_hiders + max_seekers;
     return h;
 }
 
@@ -281,6 +306,355 @@ int hsref_dump_world(void *hp, int world, hsref_world *out)
         out->leaf_obj_ids[i] = bvh.leaf_obj_ids_[i].idx;
     }
 
+    return 0;
+}
+
+
+// ---- bulk parity support -----------------------------------------------------------------------
+namespace {
+
+struct BodyIndex {
+    int n = 0;
+    madrona::Entity e[HSREF_MAX_BODIES];
+    madrona::Loc loc[HSREF_MAX_BODIES];
+    int arch[HSREF_MAX_BODIES];
+
+    void build(Engine &ctx)
+    {
+        using namespace madrona;
+        n = 0;
+        auto q = ctx.query<Entity, OwnerTeam, bp::LeafID>();
+        ctx.iterateQuery(q, [&](Entity ent, OwnerTeam &, bp::LeafID &) {
+            if (n >= HSREF_MAX_BODIES) return;
+            e[n] = ent;
+            loc[n] = ctx.loc(ent);
+            arch[n] = ctx.getSafe<GrabData>(ent).valid() ? 1 : 0;
+            n++;
+        });
+    }
+    int ofLoc(madrona::Loc l) const
+    {
+        for (int i = 0; i < n; i++)
+            if (loc[i].archetype == l.archetype && loc[i].row == l.row) return i;
+        return 255;
+    }
+    int ofEntity(madrona::Entity x) const
+    {
+        for (int i = 0; i < n; i++)
+            if (e[i] == x) return i;
+        return -1;
+    }
+};
+
+void snapCandidates(Engine &ctx, ProbeData &P)
+{
+    using namespace madrona;
+    using namespace madrona::phys;
+    BodyIndex B;
+    B.build(ctx);
+    int n = 0;
+    auto q = ctx.query<CandidateCollision>();
+    ctx.iterateQuery(q, [&](CandidateCollision &c) {
+        if (n < HSREF_C_CAND) {
+            P.cand[n][0] = (uint8_t)B.ofLoc(c.a);
+            P.cand[n][1] = (uint8_t)B.ofLoc(c.b);
+        }
+        n++;
+    });
+    P.numCand = n;
+}
+
+void snapContacts(Engine &ctx, ProbeData &P)
+{
+    using namespace madrona;
+    using namespace madrona::phys;
+    BodyIndex B;
+    B.build(ctx);
+    int n = 0;
+    auto q = ctx.query<ContactConstraint, xpbd::XPBDContactState>();
+    ctx.iterateQuery(q, [&](ContactConstraint &c, xpbd::XPBDContactState &st) {
+        if (n < HSREF_C_CONTACTS) {
+            P.ref[n] = (uint8_t)B.ofLoc(c.ref);
+            P.alt[n] = (uint8_t)B.ofLoc(c.alt);
+            P.npts[n] = (uint8_t)c.numPoints;
+            for (int p = 0; p < 4; p++) {
+                P.pts[n][p][0] = c.points[p].x; P.pts[n][p][1] = c.points[p].y;
+                P.pts[n][p][2] = c.points[p].z; P.pts[n][p][3] = c.points[p].w;
+            }
+            P.normal[n][0] = c.normal.x; P.normal[n][1] = c.normal.y; P.normal[n][2] = c.normal.z;
+            P.lambda[n] = st.lambdaN[0];
+        }
+        n++;
+    });
+    P.numContacts = n;
+}
+
+uint32_t countCandidates(Engine &ctx)
+{
+    auto q = ctx.query<madrona::phys::CandidateCollision>();
+    uint32_t n = 0;
+    ctx.iterateQuery(q, [&](madrona::phys::CandidateCollision &) { n++; });
+    return n;
+}
+
+uint32_t countContacts(Engine &ctx)
+{
+    auto q = ctx.query<madrona::phys::ContactConstraint, madrona::phys::xpbd::XPBDContactState>();
+    uint32_t n = 0;
+    ctx.iterateQuery(q, [&](madrona::phys::ContactConstraint &, madrona::phys::xpbd::XPBDContactState &) { n++; });
+    return n;
+}
+
+// The body every lidar ray hits: the ray set-up of lidarSystem (src/sim.cpp:712-759) handed to
+// the reference's own BVH::traceRay on the state the step left behind (nothing moves between the
+// lidar node and the end of the Step graph).
+void snapLidarHits(Engine &ctx, Sim &sim, ProbeData &P)
+{
+    using namespace madrona;
+    using namespace madrona::math;
+    using namespace madrona::base;
+    BodyIndex B;
+    B.build(ctx);
+    auto &bvh = ctx.singleton<bp::BVH>();
+    for (int k = 0; k < HSREF_MAX_AGENTS; k++) {
+        for (int i = 0; i < 30; i++) P.lidarHit[k][i] = -2;
+        if (k >= sim.maxAgentsPerWorld) continue;
+        Entity se = ctx.get<SimEntity>(sim.agentInterfaces[k]).e;
+        if (se == Entity::none()) continue;
+        Vector3 pos = ctx.get<Position>(se);
+        Quat rot = ctx.get<Rotation>(se);
+        Vector3 agent_fwd = rot.rotateVec(math::fwd);
+        Vector3 right = rot.rotateVec(math::right);
+        for (int32_t idx = 0; idx < 30; idx++) {
+            float theta = 2.f * math::pi * (float(idx) / float(30)) + math::pi / 2.f;
+            float x = cosf(theta);
+            float y = sinf(theta);
+            Vector3 ray_dir = (x * right + y * agent_fwd).normalize();
+            float hit_t;
+            Vector3 hit_normal;
+            Entity hit = bvh.traceRay(pos, ray_dir, &hit_t, &hit_normal, 200.f);
+            P.lidarHit[k][idx] = hit == Entity::none() ? -1 : (int8_t)B.ofEntity(hit);
+        }
+    }
+}
+
+// One world's Step graph, node by node (TaskGraph::run, M/src/core/taskgraph.cpp:164-170, is this
+// loop without the probes).  discover: learn which nodes clear the candidates / contacts.
+void runWorldProbed(Handle *h, int w, bool discover, std::vector<int> *contactClears)
+{
+    auto &exec = h->impl->cpuExec;
+    const uint32_t tg = (uint32_t)TaskGraphID::Step;
+    auto &jd = exec.job_datas_[(size_t)tg * h->numWorlds + w];
+    Engine &ctx = exec.getWorldContext(w);
+    madrona::TaskGraph &g = jd.taskgraph;
+    ProbeData &P = h->probe[w];
+    P.numCand = 0;
+    P.numContacts = 0;
+    int idx = 0;
+    for (const auto &node : g.sorted_nodes_) {
+        uint32_t candBefore = 0, conBefore = 0;
+        if (discover) {
+            candBefore = countCandidates(ctx);
+            conBefore = countContacts(ctx);
+            if (conBefore > 0) snapContacts(ctx, P);
+            if (candBefore > 0) snapCandidates(ctx, P);
+        } else {
+            if (idx == h->contactClearNode) snapContacts(ctx, P);
+            if (idx == h->candClearNode) snapCandidates(ctx, P);
+        }
+        node.fn((madrona::NodeBase *)(&g.node_datas_[node.dataIDX].userData[0]), jd.ctx, &g);
+        if (discover) {
+            if (candBefore > 0 && countCandidates(ctx) == 0) h->candClearNode = idx;
+            if (conBefore > 0 && countContacts(ctx) == 0) contactClears->push_back(idx);
+        }
+        idx++;
+    }
+    snapLidarHits(ctx, exec.getWorldData(w), P);
+}
+
+}
+
+// Manager::step() with probes: every world's Step graph is run node by node so that the
+// candidate pairs and the contacts of the last substep can be copied out just before the
+// reference clears them, and the lidar hit bodies are traced on the final state.  Worlds run on
+// `num_threads` host threads (<= 0: every core in the affinity mask); they are independent.
+// Returns 0, or -1 if the clearing nodes could not be identified.
+int hsref_step_probe(void *hp, int num_threads)
+{
+    Handle *h = (Handle *)hp;
+    const int N = h->numWorlds;
+    if (h->probe.empty()) h->probe.resize(N);
+    auto &exec = h->impl->cpuExec;
+    const uint32_t tg = (uint32_t)TaskGraphID::Step;
+    madrona::StateManager &sm = exec.job_datas_[(size_t)tg * N].taskgraph.stateManager();
+    sm.copyInExportedColumns();
+
+    // keep one instance of every query alive so worker threads never race to create them
+    auto keepA = exec.getWorldContext(0).query<madrona::phys::CandidateCollision>();
+    auto keepB = exec.getWorldContext(0).query<madrona::phys::ContactConstraint, madrona::phys::xpbd::XPBDContactState>();
+    auto keepC = exec.getWorldContext(0).query<madrona::Entity, OwnerTeam, bp::LeafID>();
+
+    int first = 0;
+    while (first < N && (h->contactClearNode < 0 || h->candClearNode < 0)) {
+        std::vector<int> clears;
+        runWorldProbed(h, first, true, &clears);
+        // four substeps (M/src/physics/xpbd.cpp:1080-1141) -> four clearing nodes, last one wins
+        if (clears.size() == 4 && h->candClearNode >= 0) {
+            h->contactClearNode = clears.back();
+        } else {
+            h->contactClearNode = -1;
+            h->probe[first].numCand = -1;       // this world's probe data is not trustworthy
+            h->probe[first].numContacts = -1;
+        }
+        first++;
+    }
+    if (h->contactClearNode < 0 || h->candClearNode < 0) {
+        sm.copyOutExportedColumns();
+        return -1;
+    }
+
+    int T = num_threads > 0 ? num_threads : hsref_affinity_cpus();
+    if (T > N - first) T = N - first > 0 ? N - first : 1;
+    std::atomic<int> next(first);
+    auto worker = [&]() {
+        for (;;) {
+            int w = next.fetch_add(1);
+            if (w >= N) break;
+            runWorldProbed(h, w, false, nullptr);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < T; t++) pool.emplace_back(worker);
+    worker();
+    for (auto &t : pool) t.join();
+
+    sm.copyOutExportedColumns();
+    return 0;
+}
+
+int hsref_compact_bytes() { return (int)sizeof(hsref_compact); }
+
+static void fillCompact(Handle *h, int world, hsref_compact *out)
+{
+    using namespace madrona;
+    using namespace madrona::phys;
+    using namespace madrona::base;
+
+    Engine &ctx = h->impl->cpuExec.getWorldContext(world);
+    Sim &sim = h->impl->cpuExec.getWorldData(world);
+    memset(out, 0, sizeof(*out));
+    out->cur_episode_step = (int32_t)sim.curEpisodeStep;
+    out->cur_world_episode = (int32_t)sim.curWorldEpisode;
+    out->rng_key[0] = sim.rng.k_.a;
+    out->rng_key[1] = sim.rng.k_.b;
+    out->rng_count = sim.rng.count_;
+    out->num_hiders = sim.numHiders;
+    out->num_seekers = sim.numSeekers;
+    out->num_boxes = (int32_t)sim.numActiveBoxes;
+    out->num_ramps = (int32_t)sim.numActiveRamps;
+    out->hider_team_reward = sim.hiderTeamReward.load_relaxed();
+    out->seekers_first = ctx.singleton<TeamState>().seekersFirst ? 1 : 0;
+    out->running_scores[0] = ctx.singleton<EpisodeStats>().runningScores[0];
+    out->running_scores[1] = ctx.singleton<EpisodeStats>().runningScores[1];
+
+    BodyIndex B;
+    B.build(ctx);
+    const int nb = B.n < HSREF_C_BODIES ? B.n : HSREF_C_BODIES;
+    out->num_bodies = B.n;
+    int nDyn = 0;
+    for (int i = 0; i < nb; i++) {
+        Entity e = B.e[i];
+        if (B.arch[i] == 0) nDyn++;
+        out->obj[i] = (uint8_t)ctx.get<ObjectID>(e).idx;
+        out->response[i] = (uint8_t)ctx.get<ResponseType>(e);
+        out->owner[i] = (uint8_t)ctx.get<OwnerTeam>(e);
+        out->leaf[i] = (uint8_t)ctx.get<bp::LeafID>(e).id;
+        int rank = 0;
+        for (int o = 0; o < nb; o++) rank += B.e[o].id < e.id;
+        out->eid_rank[i] = (uint8_t)rank;
+        Vector3 p = ctx.get<Position>(e);
+        Quat q = ctx.get<Rotation>(e);
+        Diag3x3 s = ctx.get<Scale>(e);
+        Velocity v = ctx.get<Velocity>(e);
+        Vector3 f = ctx.get<ExternalForce>(e);
+        Vector3 t = ctx.get<ExternalTorque>(e);
+        float pose[7] = {p.x, p.y, p.z, q.w, q.x, q.y, q.z};
+        memcpy(out->pose[i], pose, sizeof(pose));
+        out->scale[i][0] = s.d0; out->scale[i][1] = s.d1; out->scale[i][2] = s.d2;
+        float vel[6] = {v.linear.x, v.linear.y, v.linear.z, v.angular.x, v.angular.y, v.angular.z};
+        memcpy(out->vel[i], vel, sizeof(vel));
+        float ft[6] = {f.x, f.y, f.z, t.x, t.y, t.z};
+        memcpy(out->force[i], ft, sizeof(ft));
+    }
+    out->num_dyn = nDyn;
+    for (int k = 0; k < HSREF_MAX_AGENTS; k++) out->joint_other[k] = -1;
+    for (int i = 0, k = 0; i < nb; i++) {
+        if (B.arch[i] != 1) continue;
+        if (k < HSREF_MAX_AGENTS) {
+            Entity j = ctx.get<GrabData>(B.e[i]).constraintEntity;
+            if (j != Entity::none()) {
+                JointConstraint &jc = ctx.get<JointConstraint>(j);
+                out->joint_other[k] = (int8_t)B.ofEntity(jc.e2);
+                out->joint_sep[k] = jc.fixed.separation;
+            }
+        }
+        k++;
+    }
+
+    bp::BVH &bvh = ctx.singleton<bp::BVH>();
+    int nl = bvh.num_leaves_.load_relaxed();
+    out->bvh_num_leaves = nl;
+    out->bvh_num_nodes = (int32_t)bvh.num_nodes_;
+    int nn = std::min<int>((int)bvh.num_nodes_, HSREF_C_NODES);
+    for (int n = 0; n < nn; n++) {
+        const hsref_node *src = (const hsref_node *)&bvh.nodes_[n];
+        memcpy(out->node_bounds[n], src->bounds, sizeof(src->bounds));
+        memcpy(out->node_children[n], src->children, sizeof(src->children));
+        out->node_parent[n] = src->parent;
+    }
+    for (int i = 0; i < nl && i < HSREF_C_BODIES; i++) {
+        math::AABB a = bvh.leaf_aabbs_[i];
+        float v[6] = {a.pMin.x, a.pMin.y, a.pMin.z, a.pMax.x, a.pMax.y, a.pMax.z};
+        memcpy(out->leaf_aabb[i], v, sizeof(v));
+        out->leaf_parent[i] = bvh.leaf_parents_[i];
+    }
+
+    out->num_cand = -1;
+    out->num_contacts = -1;
+    if (!h->probe.empty()) {
+        const ProbeData &P = h->probe[world];
+        out->num_cand = P.numCand;
+        out->num_contacts = P.numContacts;
+        memcpy(out->cand, P.cand, sizeof(P.cand));
+        memcpy(out->contact_ref, P.ref, sizeof(P.ref));
+        memcpy(out->contact_alt, P.alt, sizeof(P.alt));
+        memcpy(out->contact_npts, P.npts, sizeof(P.npts));
+        memcpy(out->contact_pts, P.pts, sizeof(P.pts));
+        memcpy(out->contact_normal, P.normal, sizeof(P.normal));
+        memcpy(out->contact_lambda, P.lambda, sizeof(P.lambda));
+        memcpy(out->lidar_hit, P.lidarHit, sizeof(P.lidarHit));
+    }
+}
+
+int hsref_dump_compact(void *hp, int world0, int count, hsref_compact *out, int num_threads)
+{
+    Handle *h = (Handle *)hp;
+    if (world0 < 0 || count <= 0 || world0 + count > h->numWorlds) return -1;
+    auto keep = h->impl->cpuExec.getWorldContext(0).query<madrona::Entity, OwnerTeam, bp::LeafID>();
+    int T = num_threads > 0 ? num_threads : hsref_affinity_cpus();
+    if (T > count) T = count;
+    std::atomic<int> next(0);
+    auto worker = [&]() {
+        for (;;) {
+            int i = next.fetch_add(1);
+            if (i >= count) break;
+            fillCompact(h, world0 + i, &out[i]);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < T; t++) pool.emplace_back(worker);
+    worker();
+    for (auto &t : pool) t.join();
     return 0;
 }
 
