@@ -124,6 +124,7 @@ static int createBody(hs_sim *sim, const hs_config *cfg, int A)
                     cfg->min_hiders, cfg->max_hiders, cfg->min_seekers, cfg->max_seekers};
 
     HS_TRY(devAlloc(sim, &S.body, size_t(kBodyWords) * kMaxBodies * N));
+    HS_TRY(devAlloc(sim, &S.bodyB, size_t(kBodyAuxWords) * kMaxBodies * N));
     HS_TRY(devAlloc(sim, &S.meta, size_t(kMaxBodies) * N));
     HS_TRY(devAlloc(sim, &S.wi, size_t(WF_COUNT) * N));
     HS_TRY(devAlloc(sim, &S.wb, size_t(WB_COUNT) * N));
@@ -136,6 +137,7 @@ static int createBody(hs_sim *sim, const hs_config *cfg, int A)
     HS_TRY(devAlloc(sim, &S.cand, size_t(kMaxCand) * N));
     HS_TRY(devAlloc(sim, &S.contact, size_t(kMaxCand) * kContactWords * N));
     HS_TRY(devAlloc(sim, &S.cmeta, size_t(kMaxCand) * N));
+    HS_TRY(devAlloc(sim, &S.sched, size_t(kMaxCand) * N));
     HS_TRY(devAlloc(sim, &S.overflow, 4));
     HS_TRY(devAlloc(sim, &S.dbgLidarHit, N * A * 30));
 
@@ -180,6 +182,7 @@ static int createBody(hs_sim *sim, const hs_config *cfg, int A)
         HS_CUDA(cudaMemcpyToSymbol(c_lidarDir, dirs, sizeof(dirs)));
         HS_CUDA(cudaFuncSetAttribute(k_rays<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
         HS_CUDA(cudaFuncSetAttribute(k_rays<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
+        HS_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, solveSmemBytes(kStageMax)));
         if (const char *e = getenv("HIDESEEK_RAY_ORDER")) sim->raysNearestFirst = strcmp(e, "reference") != 0;
     }
     HS_CUDA(cudaStreamCreateWithFlags(&sim->graphStream, cudaStreamNonBlocking));
@@ -483,12 +486,20 @@ static bool fusedSolveDefault()
     const char *e = getenv("HIDESEEK_FUSED_SOLVE");
     return !(e && e[0] == '0');
 }
+// HIDESEEK_SOLVER=global: the fused solver that works out of global memory with its own level
+// schedule (k_solve_global) instead of the staged lane-pair solver (k_solve); bit-identical results.
+static bool stagedSolveDefault()
+{
+    const char *e = getenv("HIDESEEK_SOLVER");
+    return !(e && strcmp(e, "global") == 0);
+}
 
 struct Launcher {
     DeviceState S;
     cudaStream_t st;
     int count = 0;
     bool fusedSolve = fusedSolveDefault();
+    bool stagedSolve = stagedSolveDefault();
     // graph capture only: side streams + events for the independent observation-stage kernels
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t auxFork = nullptr, auxJoin[2] = {nullptr, nullptr};
@@ -578,8 +589,13 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
     for (int i = 0; i < kSubsteps; i++) {
         k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep");
         k_narrowphase<<<(L.N() + kNpWorlds - 1) / kNpWorlds, kNpThreads, sizeof(NpSmem), L.st>>>(L.S); L.mark("k_narrowphase");
-        if (L.fusedSolve) {
-            k_solve<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve");
+        if (L.fusedSolve && L.stagedSolve) {
+            // body area of the staged solver: 9 boxes + 2 ramps + ground plane + this Manager's agent slots
+            const int stageCap = kMaxBoxes + kMaxRamps + 1 + L.S.p.agentsPerWorld;
+            k_solve<<<(L.N() + kStagedGroups - 1) / kStagedGroups, kStagedThreads, solveSmemBytes(stageCap), L.st>>>(L.S, stageCap);
+            L.mark("k_solve");
+        } else if (L.fusedSolve) {
+            k_solve_global<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_global");
         } else {
             k_solve_positions<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_positions");
             k_set_velocities<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_set_velocities");

@@ -568,28 +568,17 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve_velocities(DeviceState 
 // to back.  The level schedule is built once, with the position-pass rule; it is also a valid
 // schedule for the velocity pass, whose conflicts (contacts sharing a non-Static body) are a
 // subset of the position pass's, so both passes reproduce the serial creation-order sweep.
-__global__ void __launch_bounds__(kSolveThreads) k_solve(DeviceState S)
+__device__ __noinline__ void solveWorldGlobal(const DeviceState &S, int w, SolveGroupSmem &g, int lg, unsigned gmask, int gshift)
 {
-    __shared__ SolveGroupSmem sg[kSolveGroups];
-    __shared__ unsigned long long s_static[kSolveGroups];
-    const int lane = threadIdx.x & 31;
-    const int lg = lane % kSolveLanes;
-    const int gshift = lane - lg;
-    const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
-    const int grp = threadIdx.x / kSolveLanes;
-    const int w = blockIdx.x * kSolveGroups + grp;
-    if (w >= S.p.numWorlds) return;
-    SolveGroupSmem &g = sg[grp];
     const int nb = WI(S, WF_NUM_BODIES, w);
 
     // Static bodies (never written by the velocity pass)
+    unsigned long long st = 0ull;
     {
-        unsigned long long mine = 0ull;
         for (int s = lg; s < nb; s += kSolveLanes)
-            if (metaResp(META(S, s, w)) == RESP_STATIC) mine |= 1ull << s;
+            if (metaResp(META(S, s, w)) == RESP_STATIC) st |= 1ull << s;
 #pragma unroll
-        for (int o = kSolveLanes / 2; o > 0; o >>= 1) mine |= __shfl_xor_sync(gmask, mine, o);
-        if (lg == 0) s_static[grp] = mine;
+        for (int o = kSolveLanes / 2; o > 0; o >>= 1) st |= __shfl_xor_sync(gmask, st, o);
     }
 
     int maxLvl;
@@ -615,7 +604,6 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve(DeviceState S)
     for (int s = lg; s < nb; s += kSolveLanes) setBodyVelocity(S, s, w);
     __syncwarp(gmask);
     // ---- velocity pass ----------------------------------------------------------------------------
-    const unsigned long long st = s_static[grp];
     for (int lv = 0; lv <= maxLvl; lv++) {
         const int end = K ? g.lvlStart[lv + 1] : 0;
         for (int i = g.lvlStart[lv] + lg; i < end; i += kSolveLanes) {
@@ -629,6 +617,603 @@ __global__ void __launch_bounds__(kSolveThreads) k_solve(DeviceState S)
     if (maxLvl < 0 && lg == 0)
         for (int k = 0; k < K; k++) solveContactVelocity(S, w, g.cm[k], contacts + size_t(g.cm[k] >> 24) * kContactWords, true, true);
     if (lg == 0) WI(S, WF_NUM_CONTACTS, w) = K;
+}
+
+// HIDESEEK_SOLVER=global: every world through the global-memory path (A/B against k_solve below)
+__global__ void __launch_bounds__(kSolveThreads) k_solve_global(DeviceState S)
+{
+    __shared__ SolveGroupSmem sg[kSolveGroups];
+    const int lane = threadIdx.x & 31;
+    const int lg = lane % kSolveLanes;
+    const int gshift = lane - lg;
+    const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
+    const int grp = threadIdx.x / kSolveLanes;
+    const int w = blockIdx.x * kSolveGroups + grp;
+    if (w >= S.p.numWorlds) return;
+    solveWorldGlobal(S, w, sg[grp], lg, gmask, gshift);
+}
+
+// =================================================================================================
+// Staged solver: the default k_solve.
+//
+// One launch per substep runs solvePositions + setVelocities + solveVelocities of every world, like
+// k_solve_global above, but
+//   * which bodies are carrying / Static and the object ids of every candidate pair come from
+//     k_broadphase (decided once per step, hs_trace.cuh); the group compacts the pairs that have a
+//     contact in this substep into shared memory and levels them there;
+//   * the bodies the sweep may write — the contiguous movable tail of the world, 160 B of solver
+//     records per slot — are brought into shared memory with ONE bulk-async copy per world
+//     (cp.async.bulk + mbarrier), the Gauss-Seidel sweeps read and write shared memory only, and
+//     pose + velocity go back to HBM once at the end (walls are read straight from HBM: a Static
+//     body with identity rotation is never written, its pre-solve / previous poses equal its pose
+//     and its velocities are zero);
+//   * a contact is solved by TWO lanes, one per body: every term of handleContact /
+//     solveVelocitiesForContact that belongs to one body (lever arm, world point, generalised
+//     inverse mass, the body's own update) is computed by that body's lane, the few scalars and
+//     vectors that couple them cross with __shfl_xor.  Both lanes evaluate the reference's
+//     expressions in the reference's operand order (a - b is formed as a + (-b), which is the same
+//     float), so the result is bit-identical to the one-lane code above — tests/test_solver_ab_gpu.py
+//     compares the two kernels bit for bit — at about half the instructions per contact.
+// 8 lanes = 4 lane pairs per world, 4 worlds per warp, kSolveGroups worlds per CTA.
+// =================================================================================================
+#ifndef HS_SOLVE_GROUPS
+#define HS_SOLVE_GROUPS 16
+#endif
+#ifndef HS_SOLVE_MINB
+#define HS_SOLVE_MINB 4
+#endif
+constexpr int kStagedGroups = HS_SOLVE_GROUPS;         // worlds per CTA of the staged solver
+constexpr int kStagedThreads = kStagedGroups * kSolveLanes;
+constexpr int kListCap = 48;          // contacts per world the staged path takes (more: global path)
+constexpr int kStageRecs = 4;         // staged records per body: POSE, PREV (VEL once it is derived), PRE, PREVEL
+enum StagedRec : int { SR_POSE = 0, SR_PREV = 1, SR_VEL = 1, SR_PRE = 2, SR_PREVEL = 3 };
+
+// Per-world block of the staged solver's dynamic shared memory.  The body area holds `stageCap`
+// bodies (9 boxes + 2 ramps + ground plane + the Manager's agent slots: hs_sim.cu sizes it), so the
+// struct is a header in front of it.
+struct alignas(16) StagedWorld {
+    SchedEntry list[kListCap];                   // this substep's contacts in creation order
+    unsigned long long bar;                      // mbarrier of the bulk copy
+    uint8_t order[kListCap];                     // list indices sorted by (level, creation order)
+    uint8_t lvlCount[kListCap];                  // contacts per level, then first position of the level
+    uint8_t rank[kListCap];                      // rank of a contact inside its level
+    uint8_t blvl[kStageMax + 6];                 // next free level of staged body i
+    float4 body[1][kStageRecs * 2];              // [stageCap]: records of slot first + i
+};
+__host__ __device__ constexpr int stagedWorldBytes(int stageCap)
+{
+    return (int(sizeof(StagedWorld)) + (stageCap - 1) * kStageRecs * 32 + 15) / 16 * 16;
+}
+constexpr int kMassBytes = OBJ_COUNT * 8 * 4;            // invMass, invInertia[3], muS, muD per object
+__host__ __device__ constexpr int solveSmemBytes(int stageCap) { return kMassBytes + kStagedGroups * stagedWorldBytes(stageCap); }
+static_assert(sizeof(SolveGroupSmem) <= sizeof(StagedWorld) + 11 * kStageRecs * 32, "the global path borrows the group's block");
+
+__device__ __forceinline__ uint32_t smemAddr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+constexpr unsigned kFullMask = 0xFFFFFFFFu;
+
+// Every shuffle of the staged solver runs in WARP-UNIFORM control flow with the full mask: a
+// sub-warp mask that differs between the lanes of a warp (one mask per lane pair) makes each
+// shuffle take the compiler's divergent MATCH / BRA.DIV path, which serialises the pairs and
+// costs more than the arithmetic it connects.  So the code below is written as straight-line
+// phases — per-lane work under `if (flag)` blocks that reconverge, then a full-mask exchange every
+// lane takes part in — and idle lanes simply carry zeros through the exchanges.
+__device__ __forceinline__ Vec3 shflXorV(Vec3 v)
+{
+    return {__shfl_xor_sync(kFullMask, v.x, 1), __shfl_xor_sync(kFullMask, v.y, 1), __shfl_xor_sync(kFullMask, v.z, 1)};
+}
+// v for the first body of a pair, -v for the second (x2 -= d is x2 + (-d) in IEEE arithmetic)
+__device__ __forceinline__ Vec3 signedV(Vec3 v, uint32_t signBit)
+{
+    return {__uint_as_float(__float_as_uint(v.x) ^ signBit), __uint_as_float(__float_as_uint(v.y) ^ signBit),
+            __uint_as_float(__float_as_uint(v.z) ^ signBit)};
+}
+
+__device__ __forceinline__ Pose poseOf(const float4 *rec)
+{
+    const float4 a = rec[0], b = rec[1];
+    return {{a.x, a.y, a.z}, {a.w, b.x, b.y, b.z}};
+}
+__device__ __forceinline__ Vel6 vel6Of(const float4 *rec)
+{
+    const float4 a = rec[0], b = rec[1];
+    return {{a.x, a.y, a.z}, {a.w, b.x, b.y}};
+}
+__device__ __forceinline__ void putPose(float4 *rec, Vec3 x, Quat q)
+{
+    rec[0] = make_float4(x.x, x.y, x.z, q.w);
+    rec[1] = make_float4(q.x, q.y, q.z, 0.f);
+}
+__device__ __forceinline__ void putVel6(float4 *rec, Vec3 v, Vec3 o)
+{
+    rec[0] = make_float4(v.x, v.y, v.z, o.x);
+    rec[1] = make_float4(o.y, o.z, 0.f, 0.f);
+}
+
+// one body's half of applyPositionalUpdate (xpbd.cpp:232-285)
+__device__ __forceinline__ void applyPositionalSide(Vec3 &x, Quat &q, Vec3 ra, float inv_m, Vec3 n, float lambda,
+                                                    uint32_t signBit)
+{
+    x = x + signedV((lambda * inv_m) * n, signBit);
+    const float half = 0.5f * lambda;
+    const Vec3 u = rotate(q, half * ra);
+    const Quat dq = fromAngularVec(u) * q;
+    q = q + Quat{__uint_as_float(__float_as_uint(dq.w) ^ signBit), __uint_as_float(__float_as_uint(dq.x) ^ signBit),
+                 __uint_as_float(__float_as_uint(dq.y) ^ signBit), __uint_as_float(__float_as_uint(dq.z) ^ signBit)};
+    q = qnormalize(q);
+}
+
+// What one lane of a pair needs to know about its contact and its body.
+struct PairSide {
+    int c, slot, npts;
+    bool staged, carrying;
+    float inv_m, muS, muD;          // muS / muD already averaged over the two bodies
+    Vec3 inv_I;
+    float4 *rec;                    // the body's solver records in shared memory (staged only)
+};
+
+__device__ __forceinline__ PairSide pairSide(const SchedEntry e, int side, StagedWorld &sw, int first,
+                                             const float (*mass)[8])
+{
+    PairSide p;
+    p.c = int(e.x & 0xFF);
+    p.slot = int(e.x >> (16 + 8 * side)) & 0xFF;
+    p.npts = int(e.y >> 12) & 7;
+    const int obj = int(e.y >> (4 * side)) & 15, objRef = int(e.y) & 15, objAlt = int(e.y >> 4) & 15;
+    p.carrying = (e.y >> (8 + side)) & 1;
+    const bool isStatic = (e.y >> (10 + side)) & 1;
+    p.staged = p.slot >= first;
+    p.rec = sw.body[p.staged ? p.slot - first : 0];     // the body area extends past the declared [1]
+    p.inv_m = isStatic ? 0.f : mass[obj][0];
+    p.inv_I = isStatic ? Vec3{0.f, 0.f, 0.f} : Vec3{mass[obj][1], mass[obj][2], mass[obj][3]};
+    p.muS = 0.5f * (mass[objRef][4] + mass[objAlt][4]);
+    p.muD = 0.5f * (mass[objRef][5] + mass[objAlt][5]);
+    return p;
+}
+
+// handleContact (xpbd.cpp:405-550 -> handleContactConstraint 321-403), one lane per body.
+// Called by all 32 lanes; `mine` = this lane has a contact side to solve in this round.
+__device__ __forceinline__ void pairContactPositions(const DeviceState &S, int w, const PairSide &P, int side, bool mine)
+{
+    const Vec3 zero = {0.f, 0.f, 0.f};
+    float *row = S.contact + (size_t(w) * kMaxCand + P.c) * kContactWords;
+    const uint32_t signBit = side ? 0x80000000u : 0u;
+    bool act = mine;
+    Vec3 n = zero, r = zero, x = zero, p = zero;
+    Quat q = {1.f, 0.f, 0.f, 0.f};
+    Pose prev = {zero, q};
+    if (act) {
+        const ContactView c = loadContact(row, uint32_t(P.npts) << 16);
+        Vec3 avg; float pen;
+        act = !avgContact(c, &avg, &pen);
+        if (act) {
+            Pose cur, pre;
+            if (P.staged) { cur = poseOf(P.rec + 2 * SR_POSE); pre = poseOf(P.rec + 2 * SR_PRE); prev = poseOf(P.rec + 2 * SR_PREV); }
+            else { cur = loadPose(S, REC_POSE, P.slot, w); pre = cur; prev = cur; }
+            x = cur.x;
+            q = cur.q;
+            n = c.normal;
+            // getLocalSpaceContacts: the second body's point lies `pen` below the first's along the normal
+            const Vec3 contact = side ? avg - n * pen : avg;
+            r = rotate(qinv(pre.q), contact - pre.x);
+            p = rotate(q, r) + x;
+        }
+    }
+    const Vec3 po = shflXorV(p);
+    bool push = false;
+    float d = 0.f, wgt = 0.f;
+    Vec3 ra = zero;
+    if (act) {
+        d = dot(side ? po - p : p - po, n);
+        push = d > 0;
+        if (push) {
+            const Vec3 nl = rotate(qinv(q), n);
+            const Vec3 ta = cross(r, nl);
+            ra = mulDiag(P.inv_I, ta);
+            wgt = P.inv_m + dot(ta, ra);
+        }
+    }
+    const float wo = __shfl_xor_sync(kFullMask, wgt, 1);
+    float lambda_n = 0.f;
+    Vec3 e = zero;
+    if (push) {
+        lambda_n = -d / ((side ? wo : wgt) + (side ? wgt : wo) + 0.f);
+        applyPositionalSide(x, q, ra, P.inv_m, n, lambda_n, signBit);
+        const Vec3 p_hat = rotate(prev.q, r) + prev.x;
+        p = rotate(q, r) + x;
+        e = p - p_hat;
+    }
+    const Vec3 eo = shflXorV(e);
+    bool fric = false;
+    float tmag = 0.f, wf = 0.f;
+    Vec3 t = zero, fr = zero;
+    if (push) {
+        const Vec3 dp = side ? eo - e : e - eo;
+        const Vec3 dpt = dp - dot(dp, n) * n;
+        tmag = length(dpt);
+        fric = tmag > 0.f;
+        if (fric) {
+            t = dpt / tmag;
+            const Vec3 tl = rotate(qinv(q), t);
+            const Vec3 fa = cross(r, tl);
+            fr = mulDiag(P.inv_I, fa);
+            wf = P.inv_m + dot(fa, fr);
+        }
+    }
+    const float wfo = __shfl_xor_sync(kFullMask, wf, 1);
+    if (fric) {
+        const float lambda_t = -tmag / ((side ? wfo : wf) + (side ? wf : wfo) + 0.f);
+        if (lambda_t > lambda_n * P.muS) applyPositionalSide(x, q, fr, P.inv_m, t, lambda_t, signBit);
+    }
+    if (act) {
+        if (side == 0) row[19] = lambda_n;
+        if (P.carrying) putPose(P.rec + 2 * SR_POSE, x, q);
+    }
+}
+
+// solveVelocitiesForContact (xpbd.cpp:781-1039), one lane per body; called by all 32 lanes.
+__device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int w, const PairSide &P, int side, bool mine)
+{
+    const Vec3 zero = {0.f, 0.f, 0.f};
+    const float *row = S.contact + (size_t(w) * kMaxCand + P.c) * kContactWords;
+    const uint32_t signBit = side ? 0x80000000u : 0u;
+    const float h = substepH();
+    const float gMag = sqrtf(0.f * 0.f + 0.f * 0.f + 9.8f * 9.8f);
+    const float restThreshold = 2.f * gMag * h;
+
+    bool act = mine;
+    ContactView c;
+    c.n = 0;
+    Vec3 v = zero, o = zero, n = zero, ab = zero, a = zero, ra = zero;
+    Pose pre = {zero, {1.f, 0.f, 0.f, 0.f}};
+    Quat q = pre.q;
+    float wgt = 0.f, lambdaN = 0.f;
+    if (act) {
+        c = loadContact(row, uint32_t(P.npts) << 16);
+        lambdaN = c.lambdaN;
+        Vec3 avg; float pen;
+        act = !avgContact(c, &avg, &pen);
+        if (act) {
+            Vec3 pv = zero, po = zero;
+            if (P.staged) {
+                const Vel6 vel = vel6Of(P.rec + 2 * SR_VEL), pvel = vel6Of(P.rec + 2 * SR_PREVEL);
+                v = vel.v; o = vel.w; pv = pvel.v; po = pvel.w;
+                pre = poseOf(P.rec + 2 * SR_PRE);
+                q = poseOf(P.rec + 2 * SR_POSE).q;
+            } else {
+                pre = loadPose(S, REC_POSE, P.slot, w);
+                q = pre.q;
+            }
+            n = c.normal;
+            const Vec3 contact = side ? avg - n * pen : avg;
+            const Vec3 r = rotate(qinv(pre.q), contact - pre.x);
+            const Vec3 rpre = rotate(pre.q, r);
+            ab = pv + cross(po, rpre);
+            const Vec3 rw = rotate(q, r);
+            const Vec3 ta = cross(r, rotate(qinv(q), n));
+            a = v + cross(o, rw);
+            ra = mulDiag(P.inv_I, ta);
+            wgt = P.inv_m + dot(ta, ra);
+        }
+    }
+    {
+        const Vec3 abo = shflXorV(ab);
+        const Vec3 ao = shflXorV(a);
+        const float wo = __shfl_xor_sync(kFullMask, wgt, 1);
+        if (act) {
+            // applyRestitutionVelocityUpdate
+            const float vnBar = dot(n, side ? abo - ab : ab - abo);
+            const float vn = dot(n, side ? ao - a : a - ao);
+            float e = 0.3f;
+            if (fabsf(vnBar) <= restThreshold) e = 0.f;
+            const float mag = fminf(-e * vnBar, 0) - vn;
+            const float invScale = 1.f / ((side ? wo : wgt) + (side ? wgt : wo));
+            const float imp = mag * invScale;
+            if (imp != 0.f) {
+                v = v + signedV(n * imp * P.inv_m, signBit);
+                o = o + signedV(rotate(q, imp * ra), signBit);
+            }
+        }
+    }
+
+    float penSum = 0.f;
+    for (int i = 0; i < c.n; i++) penSum += c.depth[i];
+
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const bool pt = act && i < c.n;
+        Vec3 r = zero, ai = zero;
+        if (pt) {
+            const Vec3 contact = side ? c.pts[i] - n * c.depth[i] : c.pts[i];
+            r = rotate(qinv(pre.q), contact - pre.x);
+            const Vec3 rw = rotate(q, r);
+            ai = v + cross(o, rw);
+        }
+        const Vec3 aio = shflXorV(ai);
+        // applyFrictionVelocityUpdate
+        bool go = false;
+        float vtLen = 0.f, wi = 0.f;
+        Vec3 dw = zero, fr = zero;
+        if (pt) {
+            const Vec3 rel = side ? aio - ai : ai - aio;
+            const float vn = dot(n, rel);
+            const Vec3 vt = rel - n * vn;
+            vtLen = length(vt);
+            go = vtLen != 0.f;
+            if (go) {
+                dw = vt / vtLen;
+                const Vec3 dl = rotate(qinv(q), dw);
+                const Vec3 fa = cross(r, dl);
+                fr = mulDiag(P.inv_I, fa);
+                wi = P.inv_m + dot(fa, fr);
+            }
+        }
+        const float wio = __shfl_xor_sync(kFullMask, wi, 1);
+        if (go) {
+            const float lambda = lambdaN * (c.depth[i] / penSum);
+            const float invScale = 1.f / ((side ? wio : wi) + (side ? wi : wio));
+            const float fmag = P.muD * fabsf(lambda) * invScale / h;
+            const float corrected = -fminf(fmag, vtLen);
+            const float imp = corrected * invScale;
+            if (imp != 0.f) {
+                v = v + signedV(dw * imp * P.inv_m, signBit);
+                o = o + signedV(rotate(q, imp * fr), signBit);
+            }
+        }
+    }
+
+    if (act && P.carrying) putVel6(P.rec + 2 * SR_VEL, v, o);
+}
+
+// handleJointConstraint (Fixed) on the staged records; both bodies of a grab joint are movable.
+__device__ inline void stagedFixedJoint(const DeviceState &S, int w, int k, float4 *r1, float4 *r2, const MassData &m1, const MassData &m2)
+{
+    const Pose jp1 = poseOf(r1 + 2 * SR_POSE), jp2 = poseOf(r2 + 2 * SR_POSE);
+    Vec3 x1 = jp1.x, x2 = jp2.x;
+    Quat q1 = jp1.q, q2 = jp2.q;
+    Quat a1 = {JF(S, JF_A1W, k, w), JF(S, JF_A1X, k, w), JF(S, JF_A1Y, k, w), JF(S, JF_A1Z, k, w)};
+    Quat a2 = {JF(S, JF_A2W, k, w), JF(S, JF_A2X, k, w), JF(S, JF_A2Y, k, w), JF(S, JF_A2Z, k, w)};
+    Vec3 jr1 = {JF(S, JF_R1X, k, w), JF(S, JF_R1Y, k, w), JF(S, JF_R1Z, k, w)};
+    Vec3 jr2 = {JF(S, JF_R2X, k, w), JF(S, JF_R2Y, k, w), JF(S, JF_R2Z, k, w)};
+    float sep = JF(S, JF_SEP, k, w);
+    {
+        Quat o1 = qnormalize(q1 * a1), o2 = qnormalize(q2 * a2);
+        Quat diff = o1 * qinv(o2);
+        Vec3 dq = 2.f * v3(diff.x, diff.y, diff.z);
+        float mag = length(dq);
+        if (mag > 0) {
+            dq = dq / mag;
+            Vec3 l1 = rotate(qinv(q1), dq), l2 = rotate(qinv(q2), dq);
+            Vec3 ra1 = mulDiag(m1.inv_I, l1), ra2 = mulDiag(m2.inv_I, l2);
+            float w1 = dot(l1, ra1), w2 = dot(l2, ra2);
+            float dl = -mag / (w1 + w2 + 0.f);
+            float half = 0.5f * dl;
+            Quat u1 = fromAngularVec(rotate(q1, half * ra1));
+            Quat u2 = fromAngularVec(rotate(q2, half * ra2));
+            q1 = qnormalize(q1 + u1 * q1);
+            q2 = qnormalize(q2 - u2 * q2);
+        }
+    }
+    Vec3 r1w = rotate(q1, jr1) + x1, r2w = rotate(q2, jr2) + x2;
+    Vec3 dr = r2w - r1w;
+    Quat axes = qnormalize(q1 * a1);
+    Vec3 ax = rotate(axes, v3(0, 1, 0));
+    Vec3 bx = rotate(axes, v3(1, 0, 0));
+    Vec3 cx = cross(ax, bx);
+    Vec3 corr = {0.f, 0.f, 0.f};
+    corr -= (dot(dr, ax) - sep) * ax;
+    corr -= dot(dr, bx) * bx;
+    corr -= dot(dr, cx) * cx;
+    float cmag = length(corr);
+    if (cmag > 0.f) {
+        corr = corr / cmag;
+        applyPositionalFull(x1, x2, q1, q2, jr1, jr2, m1, m2, corr, cmag, 0.f);
+    }
+    putPose(r1 + 2 * SR_POSE, x1, q1);
+    putPose(r2 + 2 * SR_POSE, x2, q2);
+}
+
+// Compacts the candidate pairs that have a contact in this substep into sw.list, in creation order
+// and oriented (reference body first — the narrowphase may have swapped the pair).  Called by all
+// 32 lanes (groups without work pass nc = 0).  Returns the number of contacts; more than kListCap
+// means the list is incomplete.
+__device__ __forceinline__ int fillContactList(const DeviceState &S, int w, StagedWorld &sw, int nc, int lg, int gshift)
+{
+    const SchedEntry *sched = S.sched + size_t(w) * kMaxCand;
+    const uint32_t *cmeta = S.cmeta + size_t(w) * kMaxCand;
+    int K = 0, pos = 0;
+    while (__any_sync(kFullMask, pos < nc)) {
+        const int i = pos + lg;
+        SchedEntry e = {0u, 0u};
+        uint32_t m = 0u;
+        if (i < nc) { e = sched[i]; m = cmeta[i]; }
+        const bool has = (m >> 16) != 0;
+        const unsigned bal = (__ballot_sync(kFullMask, has) >> gshift) & ((1u << kSolveLanes) - 1u);
+        const int k = K + __popc(bal & ((1u << lg) - 1u));
+        if (has && k < kListCap) {
+            const uint32_t a = (e.x >> 16) & 0xFF, b = e.x >> 24;
+            if ((m & 0xFF) != a) {          // the narrowphase chose b as the reference body: swap the sides
+                e.x = (e.x & 0xFFFFu) | (b << 16) | (a << 24);
+                e.y = ((e.y >> 4) & 0xFu) | ((e.y & 0xFu) << 4) | (((e.y >> 9) & 1u) << 8) | (((e.y >> 8) & 1u) << 9) |
+                      (((e.y >> 11) & 1u) << 10) | (((e.y >> 10) & 1u) << 11);
+            }
+            e.y = (e.y & 0xFFFu) | (((m >> 16) & 7u) << 12);
+            sw.list[k] = e;
+        }
+        K += __popc(bal);
+        pos += kSolveLanes;
+    }
+    return K;
+}
+
+// Dependency levels of the listed contacts (see the comment above buildLevels): level(c) = the
+// next free level of its carrying bodies; a stable counting sort by level gives sw.order.  The scan
+// is inherently serial (lane 0 of the group; K is ~17), the sort is lane-parallel.
+__device__ __forceinline__ void levelContactList(StagedWorld &sw, int K, int first, int count, int lg)
+{
+    for (int i = lg; i < kListCap; i += kSolveLanes) sw.lvlCount[i] = 0;
+    for (int i = lg; i < count; i += kSolveLanes) sw.blvl[i] = 0;
+    __syncwarp();
+    if (lg == 0 && K > 0) {
+        int maxLvl = 0;
+        for (int k = 0; k < K; k++) {
+            const SchedEntry e = sw.list[k];
+            const bool ca = (e.y >> 8) & 1, cb = (e.y >> 9) & 1;
+            const int ia = int((e.x >> 16) & 0xFF) - first, ib = int(e.x >> 24) - first;     // carrying => staged
+            const int la = ca ? sw.blvl[ia] : 0, lb = cb ? sw.blvl[ib] : 0;
+            const int lv = max(la, lb);                 // <= k < kListCap
+            sw.list[k].x = (e.x & 0xFFFF00FFu) | (uint32_t(lv) << 8);
+            sw.rank[k] = sw.lvlCount[lv]++;
+            if (ca) sw.blvl[ia] = uint8_t(lv + 1);
+            if (cb) sw.blvl[ib] = uint8_t(lv + 1);
+            maxLvl = max(maxLvl, lv);
+        }
+        int run = 0;
+        for (int l = 0; l <= maxLvl; l++) { const int n = sw.lvlCount[l]; sw.lvlCount[l] = uint8_t(run); run += n; }
+    }
+    __syncwarp();
+    for (int k = lg; k < K; k += kSolveLanes) sw.order[sw.lvlCount[(sw.list[k].x >> 8) & 0xFF] + sw.rank[k]] = uint8_t(k);
+    __syncwarp();
+}
+
+// One pass (positions or velocities) over the levelled contacts: the group's four lane pairs take
+// up to four contacts of ONE level at a time; levels in order.  Called by all 32 lanes; a round
+// ends with a warp barrier, which orders the shared-memory body updates of one level before the next.
+template <bool kVelocities>
+__device__ __forceinline__ void sweepList(const DeviceState &S, int w, StagedWorld &sw, int K, int first, int lg,
+                                          const float (*mass)[8])
+{
+    const int pair = lg >> 1, side = lg & 1;
+    int i = 0;
+    while (__any_sync(kFullMask, i < K)) {
+        const bool active = i < K;
+        const int lv = active ? int(sw.list[sw.order[i]].x >> 8) & 0xFF : 0;
+        const int j = i + pair;
+        const SchedEntry ej = sw.list[min(int(sw.order[min(j, kListCap - 1)]), kListCap - 1)];
+        const bool mine = active && j < K && (int(ej.x >> 8) & 0xFF) == lv;
+        const PairSide P = pairSide(mine ? ej : SchedEntry{0u, 0u}, side, sw, first, mass);
+        if (kVelocities) pairContactVelocities(S, w, P, side, mine);
+        else pairContactPositions(S, w, P, side, mine);
+        // the order is sorted by level: the pairs that found work are a prefix of the four
+        const unsigned took = __ballot_sync(kFullMask, mine && side == 0);
+        if (active) i += max(__popc(took & (0xFFu << (threadIdx.x & 24))), 1);
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceState S, int stageCap)
+{
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    float (*mass)[8] = reinterpret_cast<float (*)[8]>(smemRaw);
+    const int lane = threadIdx.x & 31;
+    const int lg = lane % kSolveLanes;
+    const int gshift = lane - lg;
+    const int grp = threadIdx.x / kSolveLanes;
+    const int wRaw = blockIdx.x * kStagedGroups + grp;
+    const bool live = wRaw < S.p.numWorlds;
+    const int w = live ? wRaw : 0;             // idle groups stay in the warp's control flow
+    StagedWorld &sw = *reinterpret_cast<StagedWorld *>(smemRaw + kMassBytes + grp * stagedWorldBytes(stageCap));
+
+    int first = 0, count = -1, nc = 0;
+    if (live) {
+        first = WI(S, WF_STAGE_FIRST, w);
+        count = WI(S, WF_STAGE_COUNT, w);       // < 0: range longer than any Manager's body area
+        nc = WI(S, WF_NUM_CAND, w);
+    }
+    const bool work = live && count >= 0 && count <= stageCap;
+    if (!work) nc = 0;
+    const uint32_t bar = smemAddr(&sw.bar);
+    if (work && lg == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int i = threadIdx.x; i < OBJ_COUNT; i += kStagedThreads) {
+        const ObjectData &O = c_assets.obj[i];
+        mass[i][0] = O.invMass; mass[i][1] = O.invInertia[0]; mass[i][2] = O.invInertia[1];
+        mass[i][3] = O.invInertia[2]; mass[i][4] = O.muS; mass[i][5] = O.muD;
+    }
+    __syncthreads();
+    if (live && !work) {                      // staging range too long (never in generated levels)
+        const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
+        solveWorldGlobal(S, w, *reinterpret_cast<SolveGroupSmem *>(&sw), lg, gmask, gshift);
+    }
+    __syncwarp();
+
+    // ---- stage the movable tail of the world: one bulk-async copy ---------------------------------
+    if (work && lg == 0 && count > 0) {
+        static_assert(kStageRecs == kSolverRecs && REC_POSE == SR_POSE && REC_PREV == SR_PREV && REC_PRE == SR_PRE &&
+                      REC_PREVEL == SR_PREVEL, "the staged block is a byte copy of the solver records");
+        const uint32_t bytes = uint32_t(count) * kSolverRecs * kRecWords * 4u;
+        const float *src = S.body + (size_t(w) * kMaxBodies + first) * kBodyWords;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smemAddr(&sw.body[0][0])), "l"(src), "r"(bytes), "r"(bar) : "memory");
+    }
+    // ... while it is in flight, gather and level this substep's contacts
+    int K = fillContactList(S, w, sw, nc, lg, gshift);
+    const bool tooMany = K > kListCap;              // never seen; the global path has no such limit
+    const int total = K;
+    if (tooMany) K = 0;
+    levelContactList(sw, K, first, max(count, 0), lg);
+    if (work && count > 0) {
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar) : "memory");
+    }
+    __syncwarp();
+    if (tooMany) {
+        const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
+        solveWorldGlobal(S, w, *reinterpret_cast<SolveGroupSmem *>(&sw), lg, gmask, gshift);
+    }
+    __syncwarp();
+    const bool staged = work && !tooMany;
+
+    // ---- positions ----------------------------------------------------------------------------
+    sweepList<false>(S, w, sw, K, first, lg, mass);
+    // joints in creation order (at most one Fixed joint per agent), after every contact
+    if (staged && lg == 0) {
+        const int na = WI(S, WF_NUM_AGENTS, w);
+        const int nDyn = WI(S, WF_NUM_DYN, w);
+        int lastSeq = -1;
+        for (int it = 0; it < na; it++) {
+            int best = -1, bestSeq = 0x7FFFFFFF;
+            for (int k = 0; k < na; k++) {
+                uint32_t jm = JMETA(S, k, w);
+                if (jm == 0xFFFFFFFFu) continue;
+                int seq = int(jm >> 16);
+                if (seq > lastSeq && seq < bestSeq) { bestSeq = seq; best = k; }
+            }
+            if (best < 0) break;
+            lastSeq = bestSeq;
+            const int b1 = nDyn + best, b2 = int(JMETA(S, best, w) & 0xFF);
+            stagedFixedJoint(S, w, best, sw.body[b1 - first], sw.body[b2 - first], massOf(META(S, b1, w)), massOf(META(S, b2, w)));
+        }
+    }
+    __syncwarp();
+    // ---- velocities from the position change (setVelocities, xpbd.cpp:738-779) -----------------------
+    for (int j = lg; staged && j < count; j += kSolveLanes) {
+        const float h = substepH();
+        const Pose cur = poseOf(sw.body[j] + 2 * SR_POSE), prev = poseOf(sw.body[j] + 2 * SR_PREV);
+        Quat dq;
+        if (cur.q.w != prev.q.w || cur.q.x != prev.q.x || cur.q.y != prev.q.y || cur.q.z != prev.q.z) dq = cur.q * qinv(prev.q);
+        else dq = {1.f, 0.f, 0.f, 0.f};
+        const Vec3 newOmega = (2.f / h) * v3(dq.x, dq.y, dq.z);
+        // the previous pose is not needed past this point: the velocity takes its place
+        putVel6(sw.body[j] + 2 * SR_VEL, (cur.x - prev.x) / h, dq.w > 0.f ? newOmega : -newOmega);
+    }
+    __syncwarp();
+    // ---- velocity pass ----------------------------------------------------------------------------
+    sweepList<true>(S, w, sw, K, first, lg, mass);
+    // ---- pose + velocity back to HBM ----------------------------------------------------------------
+    if (staged) {
+        for (int i = lg; i < count * 4; i += kSolveLanes) {
+            const int j = i >> 2, q = i & 3;             // two float4 of POSE, then two of VEL
+            float4 *dst = recPtr(S, q < 2 ? REC_POSE : REC_VEL, first + j, w);
+            dst[q & 1] = sw.body[j][q < 2 ? 2 * SR_POSE + q : 2 * SR_VEL + (q - 2)];
+        }
+        if (lg == 0) WI(S, WF_NUM_CONTACTS, w) = total;
+    }
 }
 
 }  // namespace hs

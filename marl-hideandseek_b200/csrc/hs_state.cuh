@@ -64,17 +64,21 @@ enum BodyField : int {
 };
 
 // ---- body records -------------------------------------------------------------------------------
-// In HBM a body is seven 32-byte records, world-major: body[world][slot][record][8 floats]
-//   R0 pose (pos3, quat4)   R1 scale3        R2 velocity (lin3, ang3)   R3 force3, torque3
-//   R4 previous pose        R5 pre-solve pose                         R6 pre-solve velocity
+// In HBM a body is seven 32-byte records, world-major, in two arrays:
+//   body [world][slot][4][8 floats]   what the XPBD solver reads at the start of a substep:
+//       R0 pose (pos3, quat4)   R1 previous pose (substep start)   R2 pre-solve pose
+//       R3 pre-solve velocity
+//   bodyB[world][slot][3][8 floats]   R4 velocity (lin3, ang3)   R5 scale3   R6 force3, torque3
 // One record = one 32-byte sector = two 128-bit accesses, so the pair-centric stages
-// (narrowphase, ordered solver, rays) move whole sectors of useful bytes per body instead of
-// one 4-byte lane of seven different sectors, and the 224 bytes of a body — hence the ~6 KB of
-// a world — are contiguous for the body-parallel stages.  BodyField indices address components
-// through recOf / compOf, so scalar code is layout-agnostic.
-constexpr int kRecWords = 8, kBodyRecs = 7, kBodyWords = kRecWords * kBodyRecs;
-enum BodyRec : int { REC_POSE = 0, REC_SCALE, REC_VEL, REC_FORCE, REC_PREV, REC_PRE, REC_PREVEL };
-HS_HD constexpr int recOf(int f) { return f < BF_SX ? 0 : f < BF_VX ? 1 : f < BF_FX ? 2 : f < BF_PREV_PX ? 3 : f < BF_PRE_PX ? 4 : f < BF_PRE_VX ? 5 : 6; }
+// (narrowphase, rays) move whole sectors of useful bytes per body.  The solver records of
+// consecutive slots are contiguous (128 B per slot, no holes), so the solver stages the movable
+// tail of a world — boxes, ramps, ground plane, agents: the slots after the walls — into shared
+// memory with ONE bulk-async copy (cp.async.bulk, hs_solver.cuh).  BodyField indices address
+// components through recOf / compOf, so scalar code is layout-agnostic.
+constexpr int kRecWords = 8, kBodyRecs = 7, kSolverRecs = 4, kAuxRecs = kBodyRecs - kSolverRecs;
+constexpr int kBodyWords = kRecWords * kSolverRecs, kBodyAuxWords = kRecWords * kAuxRecs;
+enum BodyRec : int { REC_POSE = 0, REC_PREV, REC_PRE, REC_PREVEL, REC_VEL, REC_SCALE, REC_FORCE };
+HS_HD constexpr int recOf(int f) { return f < BF_SX ? REC_POSE : f < BF_VX ? REC_SCALE : f < BF_FX ? REC_VEL : f < BF_PREV_PX ? REC_FORCE : f < BF_PRE_PX ? REC_PREV : f < BF_PRE_VX ? REC_PRE : REC_PREVEL; }
 HS_HD constexpr int compOf(int f) { return f < BF_SX ? f : f < BF_VX ? f - BF_SX : f < BF_FX ? f - BF_VX : f < BF_PREV_PX ? f - BF_FX : f < BF_PRE_PX ? f - BF_PREV_PX : f < BF_PRE_VX ? f - BF_PRE_PX : f - BF_PRE_VX; }
 
 // body meta word: obj | resp<<4 | owner<<6 | entity_id<<8 | leaf<<16
@@ -105,6 +109,7 @@ enum WorldField : int {
     WF_NUM_CAND,
     WF_DID_RESET,                       // set by the reset stage for this step
     WF_NUM_CONTACTS,                    // contacts of the last substep (statistics)
+    WF_STAGE_FIRST, WF_STAGE_COUNT,     // solver staging range [first, first + count) of this step; count < 0: too large
     WF_COUNT
 };
 
@@ -171,6 +176,12 @@ struct AssetTable {
     HullData hull[OBJ_COUNT];    // indexed by object id (agents share geometry, duplicated)
 };
 
+// what the solver needs to know about one candidate pair (written once per step by k_broadphase,
+// hs_trace.cuh; the solver adds the contact's dependency level and point count per substep)
+//   x: candidate index | level << 8 | slot a << 16 | slot b << 24
+//   y: obj a | obj b << 4 | carrying a << 8 | carrying b << 9 | static a << 10 | static b << 11
+struct alignas(8) SchedEntry { uint32_t x, y; };
+
 struct SimParams {
     int numWorlds;           // worlds this launch covers (the whole shard, or one slice of it)
     int stride;              // worlds on the shard = SoA row stride of every per-world array
@@ -184,7 +195,8 @@ struct SimParams {
 
 struct DeviceState {
     SimParams p;
-    float *body;             // [N][kMaxBodies][kBodyRecs][8]
+    float *body;             // [N][kMaxBodies][kSolverRecs][8]  pose, previous / pre-solve pose, pre-solve velocity
+    float *bodyB;            // [N][kMaxBodies][kAuxRecs][8]     velocity; scale; force + torque
     uint32_t *meta;          // [N][kMaxBodies]
     int32_t *wi;             // [WF_COUNT][N]
     uint8_t *wb;             // [WB_COUNT][N]
@@ -197,6 +209,7 @@ struct DeviceState {
     uint16_t *cand;          // [N][kMaxCand]  a | b<<8
     float *contact;          // [N][kMaxCand][kContactWords]
     uint32_t *cmeta;         // [N][kMaxCand]
+    SchedEntry *sched;       // [N][kMaxCand] per-pair solver info of this step's candidates (hs_solver.cuh)
     uint32_t *overflow;      // [1] candidate-capacity overflow counter
     int8_t *dbgLidarHit;     // [N*A][30] body slot every lidar ray hit (debugFlags bit 0), -1 miss
 
@@ -233,13 +246,14 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
     const size_t b = size_t(begin), A = size_t(S.p.agentsPerWorld);
     V.p.numWorlds = count;
     V.p.worldBase = S.p.worldBase + begin;
-    V.body += b * kMaxBodies * kBodyWords; V.meta += b * kMaxBodies; V.wi += b; V.wb += b; V.joint += b; V.jmeta += b;
+    V.body += b * kMaxBodies * kBodyWords; V.bodyB += b * kMaxBodies * kBodyAuxWords; V.meta += b * kMaxBodies; V.wi += b; V.wb += b; V.joint += b; V.jmeta += b;
     V.bvh += b * kBvhWords;
     V.dfsLeaf += b * kDfsStride;
     V.resetList += b; V.resetCount += b;
     V.cand += b * kMaxCand;
     V.contact += b * kMaxCand * kContactWords;
     V.cmeta += b * kMaxCand;
+    V.sched += b * kMaxCand;
     V.dbgLidarHit += b * A * 30;
     V.exReset += b; V.exPrepCounter += b * A; V.exAction += b * A * 5; V.exSelfObs += b * A * 13;
     V.exSelfType += b * A; V.exSelfMask += b * A; V.exAgentObs += b * A * 5 * 14;
@@ -251,9 +265,14 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
 }
 
 #if defined(__CUDACC__)
+__device__ __forceinline__ float *recBase(const DeviceState &S, int rec, int s, int w)
+{
+    return rec < kSolverRecs ? S.body + ((size_t(w) * kMaxBodies + s) * kSolverRecs + rec) * kRecWords
+                             : S.bodyB + ((size_t(w) * kMaxBodies + s) * kAuxRecs + (rec - kSolverRecs)) * kRecWords;
+}
 __device__ __forceinline__ float &BF(const DeviceState &S, int f, int s, int w)
 {
-    return S.body[((size_t(w) * kMaxBodies + s) * kBodyRecs + recOf(f)) * kRecWords + compOf(f)];
+    return recBase(S, recOf(f), s, w)[compOf(f)];
 }
 __device__ __forceinline__ uint32_t &META(const DeviceState &S, int s, int w)
 {
@@ -283,7 +302,7 @@ __device__ __forceinline__ uint32_t *BVH(const DeviceState &S, int w)
 // ---- record-granular (128-bit) access --------------------------------------------------------------
 __device__ __forceinline__ float4 *recPtr(const DeviceState &S, int rec, int s, int w)
 {
-    return reinterpret_cast<float4 *>(S.body + ((size_t(w) * kMaxBodies + s) * kBodyRecs + rec) * kRecWords);
+    return reinterpret_cast<float4 *>(recBase(S, rec, s, w));
 }
 struct Pose { Vec3 x; Quat q; };
 struct Vel6 { Vec3 v; Vec3 w; };

@@ -148,10 +148,15 @@ __device__ __forceinline__ void forEachOverlap(const uint32_t *blob, const AABB 
 // visiting order: the candidate list is exactly the sequential reference's.
 constexpr int kBroadWarps = 4;
 
+constexpr int kStageMax = 18;        // bodies the solver stages per world: 9 boxes + 2 ramps + plane + 6 agents
+
 struct alignas(16) BroadWarpSmem {
     float bounds[6][kDfsStride];     // slot bounds of the r-th visited leaf
     uint32_t meta[kDfsStride];       // meta word of the body in that leaf
     uint8_t slot[kDfsStride];
+    // per-pair solver info (see the tail of k_broadphase)
+    uint16_t cand[kMaxCand];         // the candidate pairs as written out
+    uint8_t binfo[kDfsStride];       // per body slot: obj | carrying << 4 | static << 5
 };
 
 __global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
@@ -231,9 +236,54 @@ __global__ void __launch_bounds__(kBroadWarps * 32) k_broadphase(DeviceState S)
         while (h) {
             const int r = __ffsll((long long)h) - 1;
             h &= h - 1ull;
-            if (o < kMaxCand) out[o] = uint16_t(s | (int(ws.slot[r]) << 8));
+            if (o < kMaxCand) {
+                out[o] = uint16_t(s | (int(ws.slot[r]) << 8));
+                ws.cand[o] = uint16_t(s | (int(ws.slot[r]) << 8));
+            }
             o++;
         }
+    }
+
+    // ---- what the solver needs to know about this step's pairs (hs_solver.cuh) ----------------------
+    // Which bodies are Static and which rotations are identity is fixed for the four substeps of a
+    // step, so it is decided here once: a body is "carrying" (the Gauss-Seidel sweep may change it,
+    // so contacts sharing it are ordered) unless it is Static with identity rotation — walls, the
+    // ground plane — which the reference never moves and whose quaternion it re-normalises to the
+    // same bits.  Every candidate pair gets an entry with both bodies' slot, object id and flags.
+    // The solver keeps the bodies it may write in shared memory: they are the slots from the first
+    // non-wall, non-plane or carrying body to the end of the world (walls come first in a generated
+    // level), at most kStageMax of them; a world with a longer range is solved out of global memory.
+    int firstStaged = nb;
+    for (int rd = 0; rd < 2; rd++) {
+        const int s = lane + 32 * rd;
+        if (s >= nb) continue;
+        const uint32_t m = META(S, s, w);
+        const bool isStatic = metaResp(m) == RESP_STATIC;
+        bool carrying = !isStatic;
+        if (isStatic) {
+            const Quat q = loadRot(S, s, w);
+            carrying = !(q.w == 1.f && q.x == 0.f && q.y == 0.f && q.z == 0.f);
+        }
+        const int obj = metaObj(m);
+        ws.binfo[s] = uint8_t(obj | (carrying ? 16 : 0) | (isStatic ? 32 : 0));
+        if (carrying || (obj != OBJ_WALL && obj != OBJ_PLANE)) firstStaged = min(firstStaged, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) firstStaged = min(firstStaged, __shfl_xor_sync(0xFFFFFFFFu, firstStaged, o));
+    if (lane == 0) {
+        WI(S, WF_STAGE_FIRST, w) = firstStaged;
+        WI(S, WF_STAGE_COUNT, w) = nb - firstStaged > kStageMax ? -1 : nb - firstStaged;
+    }
+    __syncwarp();
+    SchedEntry *sched = S.sched + size_t(w) * kMaxCand;
+    for (int c = lane; c < total; c += 32) {
+        const int a = ws.cand[c] & 0xFF, b = ws.cand[c] >> 8;
+        const int ia = ws.binfo[a], ib = ws.binfo[b];
+        SchedEntry e;
+        e.x = uint32_t(c) | (uint32_t(a) << 16) | (uint32_t(b) << 24);
+        e.y = uint32_t(ia & 15) | (uint32_t(ib & 15) << 4) | (uint32_t((ia >> 4) & 1) << 8) | (uint32_t((ib >> 4) & 1) << 9) |
+              (uint32_t((ia >> 5) & 1) << 10) | (uint32_t((ib >> 5) & 1) << 11);
+        sched[c] = e;
     }
 }
 
