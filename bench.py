@@ -114,31 +114,33 @@ def step_alg_bytes(A, E):
 
 
 def kernel_alg_bytes(name, A, E, C, K):
-    """Per-world algorithmic bytes of one launch of `name` (mean world: E bodies, A agents,
-    C candidates, K contacts).  Persistent inputs read once, outputs written once; BVH
-    nodes, scratch and hull tables count 0 (an ideal kernel holds them on chip)."""
-    pose, posevel = 28, 52
+    """Per-world ALGORITHMIC bytes of one launch of `name`, by SURVEY.md §8(d)'s rule: only
+    persistent state counts — per live body 52 B mutable (pose 28 + velocity 24) and 24 B
+    immutable (scale 12, object id / response / owner 12), per agent the action row and the
+    exported rows — each touched once per launch.  Everything derived (BVH nodes and leaf
+    records, candidate pairs, contact rows, previous / pre-solve scratch, forces, hull tables)
+    counts 0: an ideal kernel holds it on chip.  So the figure is a LOWER bound on the DRAM
+    traffic of a launch (asserted against the ncu capture where one exists)."""
+    pose, vel = 28, 24
     table = {
-        "k_move": A * (20 + 16 + 24),
-        "k_leaf_refit": E * (40 + 12 + 4 + 24 + 40),     # pose+scale+meta+vel in, leaf record out
+        "k_move": A * (20 + pose),                       # action row + agent pose in (force is derived)
+        "k_leaf_refit": E * (pose + 12 + 12 + 4),        # pose, linear velocity, scale, object id in
         "k_bvh_rebuild": 0,
-        "k_action": A * (20 + 20),
-        "k_broadphase": E * (24 + 4) + C * 2,
-        "k_substep": E * (posevel + 24 + 4 + pose + 2 * pose + 24),
-        "k_narrowphase": C * (2 + 2 * (40 + 4)) + K * 84,
-        # fused solvePositions + setVelocities + solveVelocities: the contact row is read once
-        "k_solve": K * (84 + 2 * (3 * pose + 4) + 2 * pose) + E * (2 * pose + 24)
-                   + K * (2 * (2 * pose + 24 + 24 + 4) + 2 * 24),
-        "k_solve_positions": K * (84 + 2 * (3 * pose + 4) + 2 * pose),
-        "k_set_velocities": E * (2 * pose + 24),
-        "k_solve_velocities": K * (84 + 2 * (2 * pose + 24 + 24 + 4) + 2 * 24),
-        "k_zero_agent_vel": A * 48,
-        "k_rewards": A * (pose + 8),
+        "k_action": A * (20 + 20),                       # action row in, consumed action row out
+        "k_broadphase": E * 4,                           # response / entity id word in
+        "k_substep": E * (pose + vel + 4 + pose),        # pose + velocity + meta in, pose out
+        "k_narrowphase": E * (pose + 12 + 4),            # pose, scale, object id in (contacts are derived)
+        "k_solve": E * (pose + 4 + pose + vel),          # pose + meta in, pose + velocity out
+        "k_solve_global": E * (pose + 4 + pose + vel),
+        "k_solve_positions": E * (pose + 4 + pose),
+        "k_set_velocities": E * (pose + vel),
+        "k_solve_velocities": E * (vel + 4 + vel),
+        "k_zero_agent_vel": A * 2 * vel,
+        "k_rewards": A * (pose + 8),                     # agent pose in, reward + done out
         "k_reset": 4,
         "k_reset_worlds": 0,
-        "k_observations": A * (13 + 70 + 153 + 28) * 4 + E * posevel,
-        # leaf records in (40 B + meta), 30 lidar floats + 16 visibility flags x4 B out
-        "k_rays": A * (120 + 64) + E * (40 + 4),
+        "k_observations": A * (13 + 70 + 153 + 28) * 4 + E * (pose + vel),
+        "k_rays": A * (pose + 120 + 64),                 # agent pose in, 30 lidar floats + 16 visibility flags out
         "k_debug_positions": 136 + 17 * 8,
     }
     return float(table.get(name, 0))
@@ -159,6 +161,21 @@ def measured_traffic(kernel):
         return t["kernels"].get(kernel), t.get("source")
     except Exception:
         return None, None
+
+
+def kernel_rooflines(kernels, peak):
+    """Adds the measured-traffic view to every kernel entry: `traffic` (ncu DRAM bytes per launch),
+    `dram_frac` = traffic / avg launch time / peak, and checks the algorithmic figure is the lower
+    bound it claims to be.  Returns the list of violations (empty when consistent)."""
+    bad = []
+    for k in kernels:
+        t, _ = measured_traffic(k["kernel"])
+        k["traffic"] = t
+        k["frac"] = k["achieved_gbs"] / peak
+        k["dram_frac"] = (t / 1e9) / (k["avg_ms"] / 1e3) / peak if t and k["avg_ms"] > 0 else None
+        if t and k["alg_bytes_per_launch"] > t * 1.02:
+            bad.append(f"{k['kernel']}: algorithmic {k['alg_bytes_per_launch']:.3g} B > measured {t:.3g} B")
+    return bad
 
 
 def dist_env():
@@ -257,7 +274,8 @@ def measure_views(args, gh, torch, dev, local, peak):
            "ms_per_launch": ms, "rays_per_s": rays / (ms / 1e3), "meshes": "built-in",
            "roofline": {"bound": "hbm", "achieved": alg / (ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
                         "frac": alg / (ms / 1e3) / 1e9 / peak, "alg_bytes_per_launch": alg,
-                        "traffic": 2.13e9, "traffic_source": "profiles/r05_views_ncu.md (ncu --set full)"}}
+                        "traffic": measured_traffic("k_agent_views")[0],
+                        "traffic_source": measured_traffic("k_agent_views")[1]}}
     try:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import views_util as vu
@@ -357,43 +375,103 @@ def run_ours(args):
     e2e_value = N * world * e2e_steps / float(e2e_s.item())
     checksum = float(h_rew.sum())
 
+    # ---- end to end with EVERY output tensor copied to the host (pinned), PCIe-bound ------------
+    out_names = ("prep_counter", "self_data", "self_type", "self_mask", "lidar", "agent_data", "box_data",
+                 "ramp_data", "visible_agents_mask", "visible_boxes_mask", "visible_ramps_mask", "reward", "done")
+    outs = [getattr(sim, n + "_tensor")().to_torch() for n in out_names]
+    h_outs = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in outs]
+    d_act = sim.action_tensor().to_torch()
+    obs_bytes = sum(t.numel() * t.element_size() for t in outs)
+    obs_steps = 24
+    for i in range(obs_steps + 2):
+        if i == 2:
+            barrier()
+            t0 = time.perf_counter()
+        h_act[:, 0:2] = tape[i % 8]
+        d_act.copy_(h_act, non_blocking=True)
+        sim.step_async(stream)
+        for src, dst in zip(outs, h_outs):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+    obs_s = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(obs_s, op=dist.ReduceOp.MAX)
+    e2e_obs_value = N * world * obs_steps / float(obs_s.item())
+
+    # ---- one FULL EPISODE, device-timed: 240 steps from wherever the run stands, so the window
+    # always holds one synchronized reset wave and the whole contact build-up (the `--steps` region
+    # above starts at a fresh init(): with few steps it only sees the cheap prep phase) -----------
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    rew_sum = torch.zeros((), device=dev, dtype=torch.float64)
+    for _ in range(240):
+        one_step()
+        rew_sum += reward.abs().sum()
+    f1.record()
+    barrier()
+    fms = torch.tensor([f0.elapsed_time(f1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(fms, op=dist.ReduceOp.MAX)
+    full_ms = float(fms.item())
+    full_value = aggregate_value(N, world, 240, full_ms)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- per-kernel device times (CUDA events between launches, same stream) ---------------
+    # ---- per-kernel device times (CUDA events between launches, same stream): `profile_steps`
+    # un-graphed steps spread evenly over one more episode, world statistics sampled with them ----
     totals, counts = {}, {}
-    for _ in range(args.profile_steps):
+    every = max(1, 240 // max(1, args.profile_steps))
+    stat_sum, samples = {"bodies": 0.0, "candidates": 0.0, "contacts": 0.0}, 0
+    for i in range(240):
         actions[:, 0:2] = torch.randint(-5, 5, (N * A, 2), dtype=torch.int32, device=dev)
-        for name, kms in sim.step_profiled(stream):
-            totals[name] = totals.get(name, 0.0) + kms
-            counts[name] = counts.get(name, 0) + 1
-    stats = sim.world_stats()
-    E, C, K = stats["bodies"], stats["candidates"], stats["contacts"]
+        if i % every == every // 2 and samples < args.profile_steps:
+            for name, kms in sim.step_profiled(stream):
+                totals[name] = totals.get(name, 0.0) + kms
+                counts[name] = counts.get(name, 0) + 1
+            st = sim.world_stats()
+            for k in stat_sum:
+                stat_sum[k] += st[k]
+            samples += 1
+        else:
+            sim.step_async(stream)
+    torch.cuda.synchronize()
+    E, C, K = (stat_sum[k] / max(1, samples) for k in ("bodies", "candidates", "contacts"))
     peak, peak_src = measured_peak_gbs()
-    step_ms_prof = sum(totals.values()) / args.profile_steps
+    step_ms_prof = sum(totals.values()) / max(1, samples)
     kernels = []
     for name in sorted(totals, key=lambda n: -totals[n]):
         avg_ms = totals[name] / counts[name]
         algb = kernel_alg_bytes(name, A, E, C, K) * N
-        kernels.append({"kernel": name, "launches_per_step": counts[name] / args.profile_steps,
+        kernels.append({"kernel": name, "launches_per_step": counts[name] / max(1, samples),
                         "avg_ms": avg_ms, "share": totals[name] / sum(totals.values()),
                         "alg_bytes_per_launch": algb,
                         "achieved_gbs": (algb / 1e9) / (avg_ms / 1e3) if avg_ms > 0 else 0.0})
+    violations = kernel_rooflines(kernels, peak)
     top = kernels[0]
     traffic, traffic_src = measured_traffic(top["kernel"])
+    per_gpu = full_value / world
     roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peak,
                 "unit": "GB/s", "frac": top["achieved_gbs"] / peak, "traffic": traffic,
-                "traffic_source": traffic_src,
+                "dram_frac": top["dram_frac"], "traffic_source": traffic_src,
                 "peak_source": peak_src, "avg_launch_ms": top["avg_ms"],
                 "share_of_step": top["share"],
                 "alg_bytes_per_launch": top["alg_bytes_per_launch"],
+                "alg_le_traffic_violations": violations,
                 "whole_step": {"alg_bytes_per_env_step": step_alg_bytes(A, E),
-                               "achieved": value / world * step_alg_bytes(A, E) / 1e9,
-                               "frac": value / world * step_alg_bytes(A, E) / 1e9 / peak},
-                "how": f"CUDA events after every launch, {args.profile_steps} un-graphed steps "
-                       f"after the timed region (sum {step_ms_prof:.3f} ms/step)"}
+                               "achieved": per_gpu * step_alg_bytes(A, E) / 1e9,
+                               "frac": per_gpu * step_alg_bytes(A, E) / 1e9 / peak,
+                               "from": "full_episode"},
+                "how": f"CUDA events after every launch of {samples} un-graphed steps spread over one "
+                       f"episode (sum {step_ms_prof:.3f} ms/step); algorithmic bytes by SURVEY.md §8(d) "
+                       "(derived data counts 0)"}
+    full_episode = {"steps": 240, "value": full_value, "unit": UNIT, "ms_per_step": full_ms / 240,
+                    "mean_bodies": E, "mean_candidates": C, "mean_contacts": K,
+                    "reward_checksum": float(rew_sum.item()),
+                    "how": "240 device-timed steps after the --steps region: one whole episode incl. its reset wave"}
 
     cpu_baseline = None
     if not args.no_cpu_baseline and world == 1:
@@ -419,12 +497,20 @@ def run_ours(args):
                                "seekers, random move actions every step, renderer off",
                    "worlds_per_gpu": N, "agents_per_world": A, "sharding": f"worlds x{world}",
                    "l2": "per-GPU state (BVH 208 MB + body records 186 MB + contacts 328 MB + exports 81 MB) exceeds the 126 MB L2",
-                   "mean_bodies": E, "mean_candidates": C, "mean_contacts": K},
+                   "mean_bodies": E, "mean_candidates": C, "mean_contacts": K,
+                   "note": "`value` times exactly --steps steps from a fresh init(); `full_episode` is the "
+                           "same metric over one whole 240-step episode (reset wave included)"},
         # bytes are whole-job totals like `value` (every rank copies its own shard's tensors)
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": R * 5 * 4 * world,
                 "d2h_bytes_per_step": R * 8 * world, "steps": e2e_steps,
                 "how": "hs_step_host: pinned host actions -> H2D, step graph, reward+done D2H, "
-                       "stream sync every step", "reward_checksum": checksum},
+                       "stream sync every step; observations stay on the device (a GPU-resident policy "
+                       "reads them through DLPack)", "reward_checksum": checksum},
+        "e2e_obs_to_host": {"value": e2e_obs_value, "unit": UNIT, "h2d_bytes_per_step": R * 5 * 4 * world,
+                            "d2h_bytes_per_step": obs_bytes * world, "steps": obs_steps,
+                            "how": "pinned host actions -> H2D, step graph, all 13 output tensors D2H into pinned "
+                                   "host buffers, sync every step (PCIe-bound)"},
+        "full_episode": full_episode,
         "gpu_launches": sim.last_step_launches() * args.steps * world,     # whole job
         "gpu_launches_per_rank": sim.last_step_launches() * args.steps,
         "launches_per_step": sim.last_step_launches(),

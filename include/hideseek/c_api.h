@@ -143,6 +143,15 @@ int hs_build_view_tex_table(const char *data_dir, void *out, int out_bytes);
 /* host only: the PNG reader used for the view textures (8-bit RGB / RGBA, non-interlaced) */
 int hs_decode_png(const char *path, int *width, int *height, uint8_t *out, int64_t cap);
 
+/* host only: the collision asset table (hs::AssetTable, csrc/hs_state.cuh — hulls as half-edge
+ * meshes with face planes, AABBs, inverse mass / inertia, friction for the 8 SimObjects) that
+ * hs_create derives from the `*_collision.obj` files of `data_dir` (the reference's data/
+ * directory; hs_create itself reads $HIDESEEK_DATA_DIR), or from the built-in hull descriptions when
+ * data_dir is NULL / "".  Replaces loadPhysicsObjects + processRigidBodyAssets
+ * (src/mgr.cpp:441-588, M/src/physics/physics_assets.cpp:1268). */
+int hs_asset_table_bytes(void);
+int hs_dump_assets(const char *data_dir, void *out, int out_bytes);
+
 /* Diagnostics / parity: flat per-world internal state (layout in
  * hideseek/debug_dump.h), number of kernels launched by the last hs_step,
  * capacity-overflow counter. */

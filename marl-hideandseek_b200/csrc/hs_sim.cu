@@ -29,7 +29,7 @@
 #include "hs_views.cuh"
 
 namespace hs {
-void buildAssetTable(AssetTable &T);
+const char *buildAssetTable(AssetTable &T, const char *dataDir);      // hs_assets.cpp
 const char *decodePngRGBA(const char *path, int *width, int *height, std::vector<uint8_t> &rgba);   // hs_view_assets.cpp
 cudaError_t launchAgentViews(const DeviceState &S, const ViewParams &P, unsigned views, cudaStream_t stream);   // hs_views.cu
 }
@@ -166,7 +166,11 @@ static int createBody(hs_sim *sim, const hs_config *cfg, int A)
     HS_TRY(devAlloc(sim, &sim->dumpDev, 1));
 
     AssetTable T;
-    buildAssetTable(T);
+    {
+        // collision hulls from the reference's data directory when one is named, else built in
+        const char *err = buildAssetTable(T, getenv("HIDESEEK_DATA_DIR"));
+        if (err[0]) { g_err = std::string("hs_create: ") + err; return 1; }
+    }
     HS_CUDA(cudaMemcpyToSymbol(c_assets, &T, sizeof(T)));
 
     {
@@ -451,6 +455,17 @@ extern "C" int hs_set_debug(hs_sim *sim, unsigned flags)
 }
 
 extern "C" int hs_world_dump_bytes(void) { return (int)sizeof(hs_world_dump); }
+
+// host-only: the collision asset table hs_create builds for `data_dir` (NULL / "" = built-in hulls)
+extern "C" int hs_asset_table_bytes(void) { return (int)sizeof(AssetTable); }
+
+extern "C" int hs_dump_assets(const char *data_dir, void *out, int out_bytes)
+{
+    if (!out || out_bytes != (int)sizeof(AssetTable)) { g_err = "hs_dump_assets: bad buffer"; return 1; }
+    const char *err = buildAssetTable(*(AssetTable *)out, data_dir);
+    if (err[0]) { g_err = std::string("hs_dump_assets: ") + err; return 1; }
+    return 0;
+}
 
 extern "C" int hs_dump_world(hs_sim *sim, int world, void *out, int out_bytes)
 {
