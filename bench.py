@@ -119,8 +119,7 @@ def kernel_alg_bytes(name, A, E, C, K):
     immutable (scale 12, object id / response / owner 12), per agent the action row and the
     exported rows — each touched once per launch.  Everything derived (BVH nodes and leaf
     records, candidate pairs, contact rows, previous / pre-solve scratch, forces, hull tables)
-    counts 0: an ideal kernel holds it on chip.  So the figure is a LOWER bound on the DRAM
-    traffic of a launch (asserted against the ncu capture where one exists)."""
+    counts 0: an ideal kernel holds it on chip."""
     pose, vel = 28, 24
     table = {
         "k_move": A * (20 + pose),                       # action row + agent pose in (force is derived)
@@ -165,17 +164,18 @@ def measured_traffic(kernel):
 
 def kernel_rooflines(kernels, peak):
     """Adds the measured-traffic view to every kernel entry: `traffic` (ncu DRAM bytes per launch),
-    `dram_frac` = traffic / avg launch time / peak, and checks the algorithmic figure is the lower
-    bound it claims to be.  Returns the list of violations (empty when consistent)."""
-    bad = []
+    `frac` = algorithmic bytes / time / peak, `dram_frac` = traffic / time / peak.  Returns the
+    kernels whose algorithmic figure exceeds the DRAM bytes ncu saw inside the launch."""
+    over = []
     for k in kernels:
         t, _ = measured_traffic(k["kernel"])
         k["traffic"] = t
         k["frac"] = k["achieved_gbs"] / peak
         k["dram_frac"] = (t / 1e9) / (k["avg_ms"] / 1e3) / peak if t and k["avg_ms"] > 0 else None
         if t and k["alg_bytes_per_launch"] > t * 1.02:
-            bad.append(f"{k['kernel']}: algorithmic {k['alg_bytes_per_launch']:.3g} B > measured {t:.3g} B")
-    return bad
+            over.append(f"{k['kernel']}: algorithmic {k['alg_bytes_per_launch']:.3g} B > DRAM bytes inside the launch "
+                        f"{t:.3g} B (stores still in the write-back L2 when the kernel ends)")
+    return over
 
 
 def dist_env():
@@ -404,10 +404,13 @@ def run_ours(args):
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
+    # reward checksum from two steps 119 apart: at most one of them lies in the 96-step
+    # preparation phase (rewards 0), whatever phase the episode starts in
     rew_sum = torch.zeros((), device=dev, dtype=torch.float64)
-    for _ in range(240):
+    for i in range(240):
         one_step()
-        rew_sum += reward.abs().sum()
+        if i in (120, 239):
+            rew_sum += reward.abs().sum()
     f1.record()
     barrier()
     fms = torch.tensor([f0.elapsed_time(f1)], device=dev, dtype=torch.float64)
@@ -460,7 +463,7 @@ def run_ours(args):
                 "peak_source": peak_src, "avg_launch_ms": top["avg_ms"],
                 "share_of_step": top["share"],
                 "alg_bytes_per_launch": top["alg_bytes_per_launch"],
-                "alg_le_traffic_violations": violations,
+                "alg_gt_traffic": violations,
                 "whole_step": {"alg_bytes_per_env_step": step_alg_bytes(A, E),
                                "achieved": per_gpu * step_alg_bytes(A, E) / 1e9,
                                "frac": per_gpu * step_alg_bytes(A, E) / 1e9 / peak,
