@@ -364,7 +364,10 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
             todo = uint64_t(__ballot_sync(0xffffffffu, keep[0])) | (uint64_t(__ballot_sync(0xffffffffu, keep[1])) << 32);
         }
         const int px = px0 + (lane % kViewTileW), py = py0 + (lane / kViewTileW);
-        if (px >= W || py >= H) continue;
+        // lanes of a partial edge tile that fall outside the image keep walking with the warp (every
+        // lane meets the warp-wide shuffle / ballots at the loop top together); they trace nothing
+        const bool inImage = px < W && py < H;
+        if (!inImage) todo = 0;
         float pu = (float(px) + 0.5f) / float(W);
         float pv = (float(py) + 0.5f) / float(H);
         Vec3 d = normalize(sm.lowerLeft + pu * sm.horizontal + pv * sm.vertical - o);
@@ -437,8 +440,10 @@ __global__ void __launch_bounds__(kViewThreads, kViewCtasPerSm) k_agent_views(De
             uint32_t b = (uint32_t)(fminf(1.f, 0.2f * c.z) * 255.f);
             rgba |= r | (g << 8) | (b << 16);
         }
-        P.depth[pix] = depth;
-        reinterpret_cast<uint32_t *>(P.rgb)[pix] = rgba;
+        if (inImage) {
+            P.depth[pix] = depth;
+            reinterpret_cast<uint32_t *>(P.rgb)[pix] = rgba;
+        }
     }
   }
 }

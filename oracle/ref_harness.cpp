@@ -39,6 +39,9 @@
 
 #include "ref_dump.h"
 
+// the reference's mesh ray tracing (header-only; M/include/madrona/mesh_bvh.hpp, mesh_bvh.inl)
+#include <madrona/mesh_bvh.hpp>
+
 // The contact solver state lives in an archetype column whose component type is private to
 // M/src/physics/xpbd.cpp:9-11; component ids are tracked by type NAME, so declaring the same
 // one-member struct under the same name lets the probe read the stored normal multiplier.
@@ -656,6 +659,113 @@ int hsref_dump_compact(void *hp, int world0, int count, hsref_compact *out, int 
     worker();
     for (auto &t : pool) t.join();
     return 0;
+}
+
+
+// ---- mesh ray tracing with the reference's own code (agent-view oracle) ------------------------------
+// The ray / triangle stage of the agent views — QBVH node slab tests in quantised space, the leaf
+// loop and Woop's watertight ray-triangle test with back-face culling — is the reference's
+// MeshBVH::traceRay / traceRayLeaf / rayTriangleIntersection (M/include/madrona/mesh_bvh.inl:79-168,
+// 319-378, 380-462), compiled here unchanged.  The reference BUILDS its MeshBVH with Embree
+// (M/src/common/mesh_bvh_builder.cpp: <embree4/rtcore.h>, an external library that is not on this
+// machine), so the tree handed to it is built here: consecutive triangles grouped 8 per leaf, four
+// children per node, every node quantised by the reference's own QBVHNode::construct
+// (mesh_bvh.hpp).  The topology decides the order triangles are visited in, not which triangle is
+// hit first.
+namespace {
+
+struct RefMesh {
+    std::vector<madrona::MeshBVH::BVHVertex> verts;
+    std::vector<madrona::QBVHNode> nodes;
+    madrona::MeshBVH bvh;
+};
+
+madrona::math::AABB triRangeAABB(const RefMesh &m, int first, int count)
+{
+    using madrona::math::AABB;
+    AABB box = AABB::point(m.verts[first * 3].pos);
+    for (int i = first * 3; i < (first + count) * 3; i++) box.expand(m.verts[i].pos);
+    return box;
+}
+
+// builds the subtree over triangles [first, first + count) into node `self`; returns its bounds
+madrona::math::AABB buildRefMeshNode(RefMesh &m, int self, int first, int count)
+{
+    using madrona::math::AABB;
+    constexpr int kLeafTris = 8, kWidth = 4;
+    AABB childBox[kWidth];
+    int32_t childIdx[kWidth];
+    uint8_t triSize[kWidth] = {0, 0, 0, 0};
+    int n = 0;
+    if (count <= kLeafTris * kWidth) {
+        for (int off = 0; off < count; off += kLeafTris, n++) {
+            int c = std::min(kLeafTris, count - off);
+            childBox[n] = triRangeAABB(m, first + off, c);
+            childIdx[n] = -(first + off) - 1;              // leaf: index of its first triangle
+            triSize[n] = (uint8_t)c;
+        }
+    } else {
+        int per = (count + kWidth - 1) / kWidth;
+        for (int off = 0; off < count; off += per, n++) {
+            int c = std::min(per, count - off);
+            int child = (int)m.nodes.size();
+            m.nodes.emplace_back();
+            childBox[n] = buildRefMeshNode(m, child, first + off, c);
+            childIdx[n] = child + 1;
+        }
+    }
+    madrona::QBVHNode node = madrona::QBVHNode::construct((uint32_t)n, childBox, childIdx);
+    for (int i = 0; i < kWidth; i++) node.triSize[i] = triSize[i];
+    m.nodes[self] = node;
+    AABB box = childBox[0];
+    for (int i = 1; i < n; i++) box = AABB::merge(box, childBox[i]);
+    return box;
+}
+
+}
+
+// tris: [n][9] object-space corners; uvs: [n][6] per-corner texture coordinates or NULL
+void *hsref_mesh_create(const float *tris, const float *uvs, int n)
+{
+    if (n <= 0) return nullptr;
+    RefMesh *m = new RefMesh();
+    m->verts.resize((size_t)n * 3);
+    for (int t = 0; t < n; t++)
+        for (int k = 0; k < 3; k++) {
+            auto &v = m->verts[(size_t)t * 3 + k];
+            v.pos = {tris[t * 9 + k * 3], tris[t * 9 + k * 3 + 1], tris[t * 9 + k * 3 + 2]};
+            v.uv = uvs ? madrona::math::Vector2{uvs[t * 6 + k * 2], uvs[t * 6 + k * 2 + 1]} : madrona::math::Vector2{0.f, 0.f};
+        }
+    m->nodes.reserve((size_t)n + 8);
+    m->nodes.emplace_back();
+    madrona::math::AABB root = buildRefMeshNode(*m, 0, 0, n);
+    m->bvh = {};
+    m->bvh.nodes = m->nodes.data();
+    m->bvh.leafMats = nullptr;
+    m->bvh.vertices = m->verts.data();
+    m->bvh.rootAABB = root;
+    m->bvh.numNodes = (uint32_t)m->nodes.size();
+    m->bvh.numLeaves = (uint32_t)n;
+    m->bvh.numVerts = (uint32_t)m->verts.size();
+    return m;
+}
+
+void hsref_mesh_destroy(void *mp) { delete (RefMesh *)mp; }
+
+// closest front-facing hit of the ray o + t d, t in [0, t_max]: out = {t, normal xyz, uv}, *tri = triangle
+int hsref_mesh_trace(void *mp, const float *o, const float *d, float t_max, float *out, int *tri)
+{
+    RefMesh *m = (RefMesh *)mp;
+    madrona::MeshBVH::HitInfo hit;
+    int32_t stack[64];
+    int32_t stackSize = 0;
+    bool ok = m->bvh.traceRay({o[0], o[1], o[2]}, {d[0], d[1], d[2]}, &hit, stack, stackSize, t_max);
+    if (!ok) return 0;
+    out[0] = hit.tHit;
+    out[1] = hit.normal.x; out[2] = hit.normal.y; out[3] = hit.normal.z;
+    out[4] = hit.uv.x; out[5] = hit.uv.y;
+    *tri = (int)hit.leafMaterialIDX;
+    return 1;
 }
 
 int hsref_world_dump_bytes() { return (int)sizeof(hsref_world); }

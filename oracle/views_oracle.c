@@ -1,11 +1,18 @@
-/* TEST INFRASTRUCTURE — CPU restatement of the agent-view ray caster.  Only tests/,
+/* TEST INFRASTRUCTURE — CPU oracle of the agent-view ray caster.  Only tests/,
  * __graft_entry__.smoke() and bench.py's cpu_baseline leg may load this; the product never does.
  *
- * PARITY UNPINNED: the reference produces these images either with a Vulkan rasteriser
- * (unavailable on this box) or with Madrona's CUDA software ray caster, which is device code
- * inside the NVRTC megakernel and cannot be built or run here.  This file restates the ray
- * caster's arithmetic in plain C, brute force (every triangle of every instance, no
- * acceleration structure), following
+ * The reference produces these images either with a Vulkan rasteriser (unavailable on this box)
+ * or with Madrona's CUDA software ray caster, which is device code inside the NVRTC megakernel
+ * and cannot be built or run here.  What CAN be run here is the reference's host-compilable mesh
+ * ray tracing, MeshBVH::traceRay (M/include/madrona/mesh_bvh.inl:79-168, 319-378, 380-462): when
+ * the test installs it with hs_oracle_set_tracer (tests/views_util.py takes it from
+ * oracle/_ref/libhs_ref.so, hsref_mesh_trace), the per-instance ray / triangle stage below IS
+ * reference code and only these parts remain a restatement (PARITY UNPINNED for them):
+ *   camera ray generation      calculateOutRay, M/src/mw/device/bvh_raycast.cpp:58-88
+ *   the instance loop          ray -> object space, t rescale, closest instance, bvh_raycast.cpp:614-633
+ *   shading                    0.2 x material colour x texture, bvh_raycast.cpp:783-797, 822-935
+ * Without a tracer installed the ray / triangle stage falls back to the brute-force restatement
+ * further down (every triangle of every instance, no acceleration structure), following
  *   calculateOutRay            M/src/mw/device/bvh_raycast.cpp:58-88
  *   computeRayIsectInfo        bvh_raycast.cpp:228-270
  *   rayTriangleIntersection    bvh_raycast.cpp:317-447 (MADRONA_MESHBVH_BACKFACE_CULLING on,
@@ -101,6 +108,17 @@ static const int *g_sub_tex = 0;
 static const uint8_t *g_tex[3] = {0, 0, 0};
 static int g_tex_w[3], g_tex_h[3];
 
+/* Optional reference tracer: fn(mesh, o, d, t_max, out {t, normal xyz, uv}, &tri) -> hit; one
+ * mesh handle per object id (NULL = no mesh).  The handles hold the same triangles as `tris`. */
+typedef int (*hs_trace_fn)(void *mesh, const float *o, const float *d, float t_max, float *out, int *tri);
+static hs_trace_fn g_trace = 0;
+static void *g_mesh[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+void hs_oracle_set_tracer(hs_trace_fn fn, void **meshes)
+{
+    g_trace = fn;
+    for (int i = 0; i < 8; i++) g_mesh[i] = (fn && meshes) ? meshes[i] : 0;
+}
+
 void hs_oracle_set_uv(const float *tri_uv, const int *sub_tex) { g_tri_uv = tri_uv; g_sub_tex = sub_tex; }
 void hs_oracle_set_texture(int idx, const uint8_t *rgba, int w, int h) { g_tex[idx] = rgba; g_tex_w[idx] = w; g_tex_h[idx] = h; }
 
@@ -154,7 +172,7 @@ int hs_oracle_render_view(const float *tris, const int *tri_sub, const int *obj_
             v3 d = nrm(sub(add(add(ll, scl(horizontal, pu)), scl(vertical, pv)), start));
             float t_max = 10000.f;
             int hit = 0, hit_obj = 0, hit_sub = 0, hit_tri = 0;
-            float hit_bary[3] = {0, 0, 0};
+            float hit_uv[2] = {0, 0};
             for (int i = 0; i < num_inst; i++) {
                 int o = inst_obj[i];
                 const float *s = inst_scale + 3 * i;
@@ -169,14 +187,29 @@ int hs_oracle_render_view(const float *tris, const int *tri_sub, const int *obj_
                 float t_scale = len(rd);
                 float tm = t_max * t_scale;
                 rd = scl(rd, 1.f / t_scale);
-                isect R = isect_info(rd);
                 int any = 0;
-                for (int t = 0; t < obj_num_tri[o]; t++) {
-                    int ti = obj_first_tri[o] + t;
-                    float th, bc[3];
-                    if (tri_hit(tris + 9 * ti, R, ro, tm, &th, bc)) {
-                        tm = th; any = 1; hit_sub = tri_sub[ti]; hit_tri = ti;
-                        hit_bary[0] = bc[0]; hit_bary[1] = bc[1]; hit_bary[2] = bc[2];
+                if (g_trace && g_mesh[o]) {
+                    /* the reference's MeshBVH::traceRay on this instance's mesh */
+                    float out[6];
+                    int tri = 0;
+                    float rof[3] = {ro.x, ro.y, ro.z}, rdf[3] = {rd.x, rd.y, rd.z};
+                    if (g_trace(g_mesh[o], rof, rdf, tm, out, &tri)) {
+                        tm = out[0]; any = 1; hit_tri = obj_first_tri[o] + tri; hit_sub = tri_sub[hit_tri];
+                        hit_uv[0] = out[4]; hit_uv[1] = out[5];
+                    }
+                } else {
+                    isect R = isect_info(rd);
+                    for (int t = 0; t < obj_num_tri[o]; t++) {
+                        int ti = obj_first_tri[o] + t;
+                        float th, bc[3];
+                        if (tri_hit(tris + 9 * ti, R, ro, tm, &th, bc)) {
+                            tm = th; any = 1; hit_sub = tri_sub[ti]; hit_tri = ti;
+                            if (g_tri_uv) {
+                                const float *uv = g_tri_uv + 6 * ti;
+                                hit_uv[0] = uv[0] * bc[0] + uv[2] * bc[1] + uv[4] * bc[2];
+                                hit_uv[1] = uv[1] * bc[0] + uv[3] * bc[1] + uv[5] * bc[2];
+                            }
+                        }
                     }
                 }
                 if (any) { t_max = tm / t_scale; hit = 1; hit_obj = o; }
@@ -188,9 +221,7 @@ int hs_oracle_render_view(const float *tris, const int *tri_sub, const int *obj_
                 float c[3] = {mc[0], mc[1], mc[2]};
                 int tex = g_sub_tex ? g_sub_tex[hit_obj * 3 + hit_sub] : -1;
                 if (tex >= 0 && g_tex[tex] && g_tri_uv) {
-                    const float *uv = g_tri_uv + 6 * hit_tri;
-                    float tu = uv[0] * hit_bary[0] + uv[2] * hit_bary[1] + uv[4] * hit_bary[2];
-                    float tv = uv[1] * hit_bary[0] + uv[3] * hit_bary[1] + uv[5] * hit_bary[2];
+                    float tu = hit_uv[0], tv = hit_uv[1];
                     float tc[3];
                     sample_tex(tex, tu, 1.f - tv, tc);
                     for (int k = 0; k < 3; k++) c[k] *= tc[k];

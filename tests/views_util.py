@@ -1,8 +1,11 @@
 """Driver for the agent-view oracle (oracle/views_oracle.c -> oracle/_ref/libviews_oracle.so).
 
-TEST INFRASTRUCTURE ONLY.  The oracle is a brute-force CPU restatement of Madrona's software
-ray caster (parity unpinned: the reference's own is device-only code); the product's
-render-mesh table is flattened into the per-object triangle lists it takes.
+TEST INFRASTRUCTURE ONLY.  The oracle's per-instance ray / triangle stage is the REFERENCE's own
+MeshBVH::traceRay (oracle/_ref/libhs_ref.so, hsref_mesh_trace: M/include/madrona/mesh_bvh.inl
+compiled unchanged) whenever that library is built — `Meshes.bind()` installs it; camera rays,
+the instance loop and shading stay a restatement (views_oracle.c header).  Without libhs_ref the
+oracle falls back to its brute-force restatement.  The product's render-mesh table is flattened
+into the per-object triangle lists both take.
 """
 import ctypes as C
 import os
@@ -70,9 +73,40 @@ class Meshes:
             for f in TEXTURE_FILES:
                 self.images.append(np.ascontiguousarray(np.array(Image.open(os.path.join(data_dir, f)).convert("RGBA"), dtype=np.uint8)))
 
+    def _ref_meshes(self):
+        """One reference MeshBVH per object (built once), or False when libhs_ref is absent."""
+        if getattr(self, "_ref", None) is None:
+            import refsim
+            if not refsim.available() or os.environ.get("HIDESEEK_VIEWS_ORACLE") == "restated":
+                self._ref = False
+            else:
+                rl = refsim.lib()
+                rl.hsref_mesh_create.restype = C.c_void_p
+                rl.hsref_mesh_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+                handles = (C.c_void_p * 8)()
+                for o in range(8):
+                    n, f = int(self.num[o]), int(self.first[o])
+                    if n == 0:
+                        continue
+                    tri = np.ascontiguousarray(self.tris[f:f + n])
+                    uv = None if self.uv is None else np.ascontiguousarray(self.uv[f:f + n])
+                    handles[o] = rl.hsref_mesh_create(tri.ctypes.data, None if uv is None else uv.ctypes.data, n)
+                self._ref = (handles, C.cast(rl.hsref_mesh_trace, C.c_void_p))
+        return self._ref
+
+    def pinned(self):
+        """True when the ray / triangle stage of renders with this mesh set is reference code."""
+        return bool(self._ref_meshes())
+
     def bind(self):
-        """Point the oracle's texturing state at this mesh set (or clear it)."""
+        """Point the oracle's tracer and texturing state at this mesh set (or clear them)."""
         l = lib()
+        l.hs_oracle_set_tracer.argtypes = [C.c_void_p, C.c_void_p]
+        ref = self._ref_meshes()
+        if ref:
+            l.hs_oracle_set_tracer(ref[1], C.cast(ref[0], C.c_void_p))
+        else:
+            l.hs_oracle_set_tracer(None, None)
         if self.uv is None:
             l.hs_oracle_set_uv(None, None)
             return
