@@ -170,6 +170,18 @@ class HideAndSeekSimulator(_native.HideAndSeekSimulator):
             fns[key] = C.cast(getattr(self._clib, sym), C.c_void_p).value
         return dict(fns=fns, opaque=struct.pack("P", self.handle()))
 
+    def jax(self, xla_gpu=True):
+        """src/bindings.cpp:118 — {'init', 'step', 'save_ckpts', 'restore_ckpts'} as jitted JAX
+        functions over XLA custom calls into the C ABI (gpu_hideseek/jax_register.py).  Raises
+        RuntimeError when jax is not installed."""
+        from . import jax_register
+        return jax_register.build(self, xla_gpu)
+
+    def jax_interface_table(self):
+        """Operand / result (name, shape, dtype) lists of the four XLA custom calls; needs no jax."""
+        from . import jax_register
+        return jax_register.interface_table(self)
+
     def last_step_launches(self):
         return self._clib.hs_last_step_launches(self._h)
 

@@ -135,6 +135,20 @@ PYBIND11_MODULE(_native, m)
             return py::make_tuple(t.t.isOnGPU() ? kDLCUDA : kDLCPU, t.t.isOnGPU() ? t.t.gpuID() : 0);
         })
         .def_property_readonly("shape", &PyTensor::shape)
+        .def_property_readonly("dtype", [](const PyTensor &t) -> std::string {
+            // numpy / jax.numpy dtype name (JAXModule::getDType, M/src/python/bindings.cpp:107-135)
+            using ET = madrona::py::TensorElementType;
+            switch (t.t.type()) {
+            case ET::UInt8: return "uint8";
+            case ET::Int8: return "int8";
+            case ET::Int16: return "int16";
+            case ET::Int32: return "int32";
+            case ET::Int64: return "int64";
+            case ET::Float16: return "float16";
+            case ET::Float32: return "float32";
+            }
+            return "unknown";
+        })
         .def("device_ptr", [](const PyTensor &t) { return (uintptr_t)t.t.devicePtr(); })
         .def("gpu_id", [](const PyTensor &t) { return t.t.gpuID(); });
 
@@ -211,10 +225,9 @@ PYBIND11_MODULE(_native, m)
         .def("save_checkpoint", &Manager::saveCheckpoint)
         .def("load_checkpoint", &Manager::loadCheckpoint)
         .def("load_checkpoints", &Manager::loadCheckpoints)
-        .def("jax", [](Manager &, bool) -> py::object {
-            throw std::runtime_error("jax interface: jax / XLA are not installed in this environment "
-                                     "(SURVEY.md §8f-1; use the DLPack tensors with PyTorch)");
-        })
+        // `jax(xla_gpu)` (src/bindings.cpp:118, JAXInterface::buildEntry) is provided by the Python
+        // layer: gpu_hideseek.HideAndSeekSimulator.jax -> gpu_hideseek/jax_register.py, which
+        // registers the hs_xla_gpu_* entry points of the C ABI as XLA custom calls.
         // TrainInterface (src/mgr.cpp:1338-1375) as nested dicts of named tensors, in the
         // reference's order (Python dicts keep insertion order)
         .def("train_interface", [](py::object self) {

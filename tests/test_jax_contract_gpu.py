@@ -41,8 +41,15 @@ def test_train_interface_names():
     assert list(ti["step_outputs"]["pbt"]) == ["episode_results"]
     assert ti["step_outputs"]["rewards"].shape == (N * 6, 1)
     assert ti["checkpointing"]["checkpoint_data"].shape[0] == N
-    with pytest.raises(RuntimeError):
-        sim.jax(True)           # jax / XLA unavailable on this box
+    # the lowering's operand / result table: from the live TrainInterface == from the configuration
+    from gpu_hideseek import jax_register
+    assert sim.jax_interface_table() == jax_register.expected_interface_table(N, 6, sim.ckpt_tensor().shape[1])
+    import importlib.util
+    if importlib.util.find_spec("jax") is None:
+        with pytest.raises(RuntimeError, match="jax is not installed"):
+            sim.jax(True)       # the registration needs jax itself; everything it registers is tested below
+    with pytest.raises(RuntimeError, match="no CPU backend"):
+        sim.jax(False)
 
 
 def test_xla_buffers_equal_manager_api():
