@@ -24,7 +24,7 @@ constexpr int kMaxBoxes = 9;
 constexpr int kMaxRamps = 2;
 constexpr int kMaxWalls = 33;      // src/geo_gen.cpp:145,430-433
 constexpr int kMaxNodes = 69;      // BVH::numInternalNodes(52), broadphase.cpp:38-45
-constexpr int kMaxCand = 256;
+constexpr int kMaxCand = 128;     // candidate pairs per world; largest seen over every tested configuration: 86 (overflow is counted)
 constexpr int kIdPool = 64;        // ids_per_cache_ (id_map.hpp)
 constexpr int kCheckpointBytes = 1392;   // sizeof(Checkpoint), src/sim.hpp:283-313
 
