@@ -163,6 +163,16 @@ int hs_world_dump_bytes(void);
 int hs_compact_dump_bytes(void);
 int hs_dump_compact(hs_sim *sim, int world0, int count, void *out, int64_t out_bytes);
 int hs_set_debug(hs_sim *sim, unsigned flags);
+/* Allocation-free variant of hs_dump_compact.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments and same records as
+ * hs_dump_compact, but the device-side staging scratch is a static device array of the library
+ * (hs_dump_compact_noalloc_max() = 64 records, 1.5 MB held by every GPU that loads the library)
+ * instead of a cudaMalloc'ed buffer: the call makes no cudaMalloc / cudaFree / allocating library
+ * call.  count above the maximum is rejected with an error.  All calls share the array (it is
+ * cleared as far as a call uses it): calls that overlap on the GPU race — serialise them. */
+int hs_dump_compact_noalloc_max(void);
+int hs_dump_compact_noalloc(hs_sim *sim, int world0, int count, void *out, int64_t out_bytes);
 int hs_last_step_launches(hs_sim *sim);
 int hs_overflow_count(hs_sim *sim, uint32_t *out);
 

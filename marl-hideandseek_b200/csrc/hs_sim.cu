@@ -441,6 +441,53 @@ extern "C" int hs_dump_compact(hs_sim *sim, int world0, int count, void *out, in
     return 0;
 }
 
+// ---- allocation-free variant of hs_dump_compact ------
+// hs_dump_compact stages the records in a cudaMalloc'ed scratch buffer, which callers under CUDA
+// graph capture, tight serving loops or harnesses that forbid allocation cannot afford.  This
+// variant stages them in a file-scope device array instead: kNoAllocDumpMax records (1.5 MB) that
+// every GPU loading the library holds until exit.  The array's NAME is a host-side stand-in in
+// host code, not a device address, so the device address is fetched once per device, with that
+// device current, by cudaGetSymbolAddress and that pointer is what the kernel is given.
+// Every call shares the array and it keeps the last call's contents: the part a call uses is
+// cleared first (k_dump_compact does not write every byte of a record), and calls that overlap on
+// the GPU — two host threads, two simulators on one device — race on it.
+constexpr int kNoAllocDumpMax = 64;
+static __device__ __align__(256) unsigned char g_noAllocDumpScratch[kNoAllocDumpMax * sizeof(hs_compact_world)];
+constexpr int kNoAllocMaxDevices = 64;
+static void *g_noAllocDumpAddr[kNoAllocMaxDevices] = {};
+
+extern "C" int hs_dump_compact_noalloc_max(void) { return kNoAllocDumpMax; }
+
+extern "C" int hs_dump_compact_noalloc(hs_sim *sim, int world0, int count, void *out, int64_t out_bytes)
+{
+    if (!sim || !out || world0 < 0 || count <= 0 || world0 + count > sim->cfg.num_worlds ||
+        out_bytes < (int64_t)count * (int64_t)sizeof(hs_compact_world)) {
+        g_err = "hs_dump_compact_noalloc: bad argument";
+        return 1;
+    }
+    if (count > kNoAllocDumpMax) {
+        g_err = "hs_dump_compact_noalloc: count " + std::to_string(count) + " exceeds the static scratch: at most " +
+                std::to_string(kNoAllocDumpMax) + " worlds per call (use hs_dump_compact, or several calls)";
+        return 1;
+    }
+    const int dev = sim->cfg.gpu_id;
+    if (dev < 0 || dev >= kNoAllocMaxDevices) { g_err = "hs_dump_compact_noalloc: device index out of range"; return 1; }
+    HS_CUDA(cudaSetDevice(dev));
+    if (!g_noAllocDumpAddr[dev]) {           // once per device, with that device current
+        void *p = nullptr;
+        HS_CUDA(cudaGetSymbolAddress(&p, g_noAllocDumpScratch));
+        g_noAllocDumpAddr[dev] = p;
+    }
+    hs_compact_world *scratch = (hs_compact_world *)g_noAllocDumpAddr[dev];
+    const size_t bytes = size_t(count) * sizeof(hs_compact_world);
+    HS_CUDA(cudaDeviceSynchronize());
+    HS_CUDA(cudaMemsetAsync(scratch, 0, bytes, nullptr));
+    k_dump_compact<<<count, 64>>>(sim->S, world0, scratch);
+    HS_CUDA(cudaGetLastError());
+    HS_CUDA(cudaMemcpy(out, scratch, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 extern "C" int hs_set_debug(hs_sim *sim, unsigned flags)
 {
     if (!sim) { g_err = "hs_set_debug: null sim"; return 1; }
