@@ -29,6 +29,9 @@ namespace hs {
 #endif
 constexpr int kRayThreads = 160;
 constexpr int kMaxVisRays = kMaxAgents * (kMaxBoxes + kMaxRamps + kMaxAgents - 1);   // 96
+constexpr int kMaxRays = kMaxAgents * 30 + kMaxVisRays;                               // 276 per world
+constexpr int kRayQueueA = 1024, kRayQueueB = 384;
+static_assert(kMaxRays <= 512 && kMaxBodies <= 64, "queue entries pack a ray in 9 bits and a leaf in 6");
 
 __constant__ float c_lidarDir[30][2];     // (cos, sin) of theta_i, hs_det_sincosf on the host
 
@@ -45,6 +48,13 @@ struct RaySmem {
     uint16_t visInfo[kMaxVisRays];        // agent k | target slot << 3 | seesHiderCandidate << 11
     float *visOut[kMaxVisRays];
     int numVis;
+    unsigned long long leafBar;           // mbarrier of the leaf-tile bulk copy
+    // queued query (k_rays, nearest-first mode): per-ray state + the two CTA-wide work lists
+    unsigned long long rayKey[kMaxRays];  // closest hit so far: float bits of t << 32 | (0x7FFFFFFF - leaf); low word ~0 = none
+    float rayD[kMaxRays][3], rayInv[kMaxRays][3];
+    uint16_t qa[kRayQueueA];              // (ray | leaf << 9): slab-entered leaves still to be re-checked
+    uint16_t qb[kRayQueueB];              // (ray | leaf << 9): leaves whose hull has to be intersected
+    int qaCount, qbCount;
 };
 
 // Ray vs one leaf in object space; operand order of hs_trace.cuh::traceLeaf, tables in shared.
@@ -280,6 +290,57 @@ __device__ inline int traceRayFlat(const uint32_t *blob, const AssetTable &AT, b
     return int(blob[kBvhLeafOff + hitLeaf * kLeafWords + kLeafInfo] & 0xFF);
 }
 
+// ---- queued flat query (what k_rays runs in nearest-first mode) -------------------------------------
+// traceRayFlat above leaves every ray's follow-up work — the leaves its ray enters besides the
+// nearest one — to the ray's own lane: a few rays per warp have long candidate lists, so the
+// re-checks ran at ~6 and the hull tests at ~2.6 of 32 lanes and cost more than the first tests.
+// The closest hit is a MINIMUM over leaves (a leaf's hit distance does not depend on the bound it
+// is tested with; the bound only prunes), so the follow-up work of all rays of a world is put on
+// two CTA-wide lists and done at full lanes: list A = (ray, leaf) slab re-checks against the
+// ray's best hit so far, list B = the survivors' hull tests; results merge with atomicMin on a
+// packed (t, leaf) key per ray.  A full list falls back to doing the item in place.
+__device__ __forceinline__ unsigned long long rayKeyPack(float t, int leaf)
+{
+    return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(0x7FFFFFFFu - (unsigned)leaf);
+}
+__device__ __forceinline__ unsigned long long rayKeyNone(float tmax)
+{
+    return ((unsigned long long)__float_as_uint(tmax) << 32) | 0xFFFFFFFFull;
+}
+__device__ __forceinline__ float rayKeyT(unsigned long long k) { return __uint_as_float((unsigned)(k >> 32)); }
+
+__device__ __forceinline__ bool leafSlab(const float *L, Vec3 o, Vec3 inv, float t_max, float *entry)
+{
+    float tlx = inv.x * (L[0] - o.x), tly = inv.y * (L[1] - o.y), tlz = inv.z * (L[2] - o.z);
+    float tux = inv.x * (L[3] - o.x), tuy = inv.y * (L[4] - o.y), tuz = inv.z * (L[5] - o.z);
+    float mnx = fminf(tlx, tux), mny = fminf(tly, tuy), mnz = fminf(tlz, tuz);
+    float mxx = fmaxf(tlx, tux), mxy = fmaxf(tly, tuy), mxz = fmaxf(tlz, tuz);
+    const float a = fmaxf(mnx, fmaxf(mny, fmaxf(mnz, 0.f)));
+    *entry = a;
+    return a <= fminf(mxx, fminf(mxy, fminf(mxz, t_max)));
+}
+
+// hull test of (ray r, leaf) merged into the ray's key; `o` = the ray's origin
+__device__ __forceinline__ void rayTestLeaf(RaySmem &sm, int r, int leaf, Vec3 o)
+{
+    const Vec3 d = {sm.rayD[r][0], sm.rayD[r][1], sm.rayD[r][2]};
+    const float best = rayKeyT(*(volatile unsigned long long *)&sm.rayKey[r]);
+    float t;
+    if (traceLeafS(sm.bvh, sm.assets, leaf, o, d, best, &t)) atomicMin(&sm.rayKey[r], rayKeyPack(t, leaf));
+}
+
+// slab re-check of (ray r, leaf) against the ray's best hit so far; survivors go to list B
+__device__ __forceinline__ void rayRecheckLeaf(RaySmem &sm, int r, int leaf, Vec3 o)
+{
+    const Vec3 inv = {sm.rayInv[r][0], sm.rayInv[r][1], sm.rayInv[r][2]};
+    const float best = rayKeyT(*(volatile unsigned long long *)&sm.rayKey[r]);
+    float a;
+    if (!leafSlab(leafF(sm.bvh, leaf), o, inv, best, &a)) return;
+    const int i = atomicAdd(&sm.qbCount, 1);
+    if (i < kRayQueueB) sm.qb[i] = uint16_t(r | (leaf << 9));
+    else rayTestLeaf(sm, r, leaf, o);
+}
+
 // kNearestFirst = false walks the BVH in the reference's visiting order (ties resolved
 // identically); true is the flat nearest-first query and the default (hs_sim.cu: HIDESEEK_RAY_ORDER=reference selects the other at run time).
 template <bool kNearestFirst>
@@ -308,8 +369,22 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
         // the flat query never touches the inner nodes: header only
         const int nodeVec = kNearestFirst ? kBvhNodeOff / 4 : (kBvhNodeOff + numNodes * kNodeWords) / 4;
         for (int i = tid; i < nodeVec; i += kRayThreads) dst[i] = src[i];
-        const int leafVec0 = kBvhLeafOff / 4, leafVec = (numLeaves * kLeafWords) / 4;
-        for (int i = tid; i < leafVec; i += kRayThreads) dst[leafVec0 + i] = src[leafVec0 + i];
+        // the world's leaf records are one contiguous, 16-byte aligned run of numLeaves * 80 bytes:
+        // ONE bulk-async copy (TMA engine), completion counted on an mbarrier; it overlaps the
+        // staging of the asset table and the agent poses below
+        static_assert((kBvhLeafOff * 4) % 16 == 0 && (kLeafWords * 4) % 16 == 0 && (kBvhWords * 4) % 16 == 0, "bulk copy alignment");
+        if (tid == 0) {
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sm.leafBar);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            if (numLeaves > 0) {
+                const uint32_t bytes = uint32_t(numLeaves) * kLeafWords * 4u;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"((uint32_t)__cvta_generic_to_shared(sm.bvh + kBvhLeafOff)), "l"(g + kBvhLeafOff), "r"(bytes), "r"(bar)
+                             : "memory");
+            }
+        }
         const uint32_t *ca = reinterpret_cast<const uint32_t *>(&c_assets);
         uint32_t *sa = reinterpret_cast<uint32_t *>(&sm.assets);
         for (int i = tid; i < int(sizeof(AssetTable) / 4); i += kRayThreads) sa[i] = ca[i];
@@ -327,6 +402,13 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
     }
     if (tid == 0) sm.numVis = 0;
     __syncthreads();
+    if (numLeaves > 0) {                     // leaf tile landed?
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sm.leafBar);
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar) : "memory");
+    }
     if (tid < A) {
         int skip = -1;
         if (sm.agentSlot[tid] >= 0) {
@@ -383,6 +465,111 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
     const int numLidar = A * 30;
     const int numRays = numLidar + sm.numVis;
     const int rounded = (numRays + 31) & ~31;
+    if (kNearestFirst) {
+        if (tid == 0) { sm.qaCount = 0; sm.qbCount = 0; }
+        __syncthreads();
+        // ---- stage 1, lane = ray: slab-test every leaf, intersect the nearest-entry leaf's hull,
+        //      queue the other entered leaves ----------------------------------------------------------
+        for (int r = tid; r < numRays; r += kRayThreads) {
+            Vec3 d = {1.f, 0.f, 0.f};
+            float tmax = 0.f;
+            int k;
+            bool active = true;
+            if (r < numLidar) {
+                k = r / 30;
+                const int i = r - k * 30;
+                if (sm.agentSlot[k] < 0) {
+                    active = false;
+                } else {
+                    Quat rot = {sm.agentRot[k][0], sm.agentRot[k][1], sm.agentRot[k][2], sm.agentRot[k][3]};
+                    Vec3 fwd = rotate(rot, v3(0, 1, 0));
+                    Vec3 right = rotate(rot, v3(1, 0, 0));
+                    float x = c_lidarDir[i][0], y = c_lidarDir[i][1];
+                    d = normalize(x * right + y * fwd);
+                    tmax = 200.f;
+                }
+            } else {
+                const int q = r - numLidar;
+                k = sm.visInfo[q] & 7;
+                d = {sm.visDir[q][0], sm.visDir[q][1], sm.visDir[q][2]};
+                tmax = 1.f;
+            }
+            unsigned long long key = rayKeyNone(tmax);
+            if (active) {
+                const Vec3 o = {sm.agentPos[k][0], sm.agentPos[k][1], sm.agentPos[k][2]};
+                const Vec3 inv = {1.f / d.x, 1.f / d.y, 1.f / d.z};
+                const int skipLeaf = sm.agentSkipLeaf[k];
+                unsigned long long mask = 0ull;
+                float bestA = INFINITY;
+                int bestL = -1;
+                for (int l = 0; l < numLeaves; l++) {
+                    float a;
+                    const bool ok = leafSlab(leafF(sm.bvh, l), o, inv, tmax, &a);
+                    if (ok && l != skipLeaf) {
+                        mask |= 1ull << l;
+                        if (a < bestA) { bestA = a; bestL = l; }
+                    }
+                }
+                if (bestL >= 0) {
+                    float t;
+                    if (traceLeafS(sm.bvh, sm.assets, bestL, o, d, tmax, &t)) key = rayKeyPack(t, bestL);
+                    mask &= ~(1ull << bestL);
+                }
+                sm.rayD[r][0] = d.x; sm.rayD[r][1] = d.y; sm.rayD[r][2] = d.z;
+                sm.rayInv[r][0] = inv.x; sm.rayInv[r][1] = inv.y; sm.rayInv[r][2] = inv.z;
+                sm.rayKey[r] = key;
+                if (mask) {
+                    int pos = atomicAdd(&sm.qaCount, __popcll(mask));
+                    for (; mask; mask &= mask - 1ull, pos++) {
+                        const int l = __ffsll((long long)mask) - 1;
+                        if (pos < kRayQueueA) sm.qa[pos] = uint16_t(r | (l << 9));
+                        else rayRecheckLeaf(sm, r, l, o);              // list full: in place
+                    }
+                }
+            } else {
+                sm.rayKey[r] = key;
+            }
+        }
+        __syncthreads();
+        // ---- stage 2, lane = queued (ray, leaf): slab re-check against the ray's best hit ----------
+        const int nA = min(sm.qaCount, kRayQueueA);
+        for (int i = tid; i < nA; i += kRayThreads) {
+            const int e = sm.qa[i], r = e & 511, l = e >> 9;
+            const int k = r < numLidar ? r / 30 : (sm.visInfo[r - numLidar] & 7);
+            rayRecheckLeaf(sm, r, l, {sm.agentPos[k][0], sm.agentPos[k][1], sm.agentPos[k][2]});
+        }
+        __syncthreads();
+        // ---- stage 3, lane = surviving (ray, leaf): hull intersection, merged by atomicMin ----------
+        const int nB = min(sm.qbCount, kRayQueueB);
+        for (int i = tid; i < nB; i += kRayThreads) {
+            const int e = sm.qb[i], r = e & 511, l = e >> 9;
+            const int k = r < numLidar ? r / 30 : (sm.visInfo[r - numLidar] & 7);
+            rayTestLeaf(sm, r, l, {sm.agentPos[k][0], sm.agentPos[k][1], sm.agentPos[k][2]});
+        }
+        __syncthreads();
+        // ---- results ------------------------------------------------------------------------------------
+        for (int r = tid; r < numRays; r += kRayThreads) {
+            const unsigned long long key = sm.rayKey[r];
+            const unsigned low = (unsigned)key;
+            const int hit = low == 0xFFFFFFFFu ? -1
+                          : int(sm.bvh[kBvhLeafOff + int(0x7FFFFFFFu - low) * kLeafWords + kLeafInfo] & 0xFF);
+            const float t = rayKeyT(key);
+            if (r < numLidar) {
+                const int k = r / 30;
+                if (sm.agentSlot[k] < 0) continue;
+                S.exLidar[(size_t(w) * A + k) * 30 + (r - k * 30)] = hit < 0 ? 0.f : t;
+                if (S.p.debugFlags & 1u) S.dbgLidarHit[(size_t(w) * A + k) * 30 + (r - k * 30)] = int8_t(hit);
+            } else {
+                const int q = r - numLidar;
+                const int info = sm.visInfo[q];
+                const bool vis = hit == ((info >> 3) & 0xFF);
+                *sm.visOut[q] = vis ? 1.f : 0.f;
+                // CPU-backend side effect (src/sim.cpp:700-705)
+                if (vis && (info >> 11)) WI(S, WF_HIDER_REWARD, w) = __float_as_int(-1.f);
+            }
+        }
+        return;
+    }
     for (int r = tid; r < rounded; r += kRayThreads) {
         bool active = r < numRays;
         Vec3 o = {0.f, 0.f, 0.f}, d = {1.f, 0.f, 0.f};

@@ -204,3 +204,66 @@ def shard_worlds(total_worlds, num_shards):
         out.append((base, n))
         base += n
     return out
+
+
+class ShardedSimulator:
+    """One simulator object over several GPUs of one process: `num_worlds` worlds
+    are cut into contiguous shards (shard_worlds), one HideAndSeekSimulator per entry of `gpu_ids`
+    with `world_base` set so that the episode RNG stays keyed by GLOBAL world index — results are
+    those of one big simulator.  Worlds never interact, so there is no collective: `step()` launches
+    every shard's step graph on its device's default stream from this thread, then waits for all
+    of them.  A `*_tensor()` getter returns the LIST of per-shard tensors (a contiguous cross-GPU
+    tensor does not exist); `worlds` gives each shard's [base, base + count).  The reference has
+    no multi-GPU mode (`gpuID` is a single device)."""
+
+    def __init__(self, gpu_ids, num_worlds, **kwargs):
+        if not gpu_ids:
+            raise ValueError("ShardedSimulator: gpu_ids is empty")
+        for k in ("gpu_id", "world_base"):
+            if k in kwargs:
+                raise ValueError(f"ShardedSimulator: {k} is set per shard")
+        self.gpu_ids = [int(g) for g in gpu_ids]
+        self.worlds = shard_worlds(int(num_worlds), len(self.gpu_ids))
+        self.num_worlds = int(num_worlds)
+        self.shards = [HideAndSeekSimulator(gpu_id=g, num_worlds=n, world_base=b, **kwargs)
+                       for g, (b, n) in zip(self.gpu_ids, self.worlds) if n > 0]
+
+    def init(self):
+        for s in self.shards:
+            s.init()
+
+    def step_async(self):
+        for s in self.shards:
+            s.step_async(0)
+
+    def sync(self):
+        for s in self.shards:
+            s.sync(0)
+
+    def step(self):
+        self.step_async()
+        self.sync()
+
+    def overflow_count(self):
+        return sum(s.overflow_count() for s in self.shards)
+
+    def __getattr__(self, name):
+        # tensor getters and per-world pokes of the reference API, fanned out
+        if name.endswith("_tensor"):
+            return lambda: [getattr(s, name)() for s in self.shards]
+        raise AttributeError(name)
+
+    def _locate(self, world):
+        for s, (b, n) in zip(self.shards, [w for w in self.worlds if w[1] > 0]):
+            if b <= world < b + n:
+                return s, world - b
+        raise IndexError(f"world {world} out of range")
+
+    def trigger_reset(self, world, level=1):
+        s, w = self._locate(world)
+        s.trigger_reset(w, level)
+
+    def set_action(self, agent_row, x, y, r, g=False, l=False):
+        A = self.shards[0].agents_per_world
+        s, w = self._locate(agent_row // A)
+        s.set_action(w * A + agent_row % A, x, y, r, g, l)
