@@ -674,9 +674,11 @@ enum StagedRec : int { SR_POSE = 0, SR_PREV = 1, SR_VEL = 1, SR_PRE = 2, SR_PREV
 struct alignas(16) StagedWorld {
     SchedEntry list[kListCap];                   // this substep's contacts in creation order
     unsigned long long bar;                      // mbarrier of the bulk copy
-    uint8_t order[kListCap];                     // list indices sorted by (level, creation order)
-    uint8_t lvlCount[kListCap];                  // contacts per level, then first position of the level
-    uint8_t rank[kListCap];                      // rank of a contact inside its level
+    uint8_t order[kListCap];                     // list indices sorted by (level, doubles before singles, creation order)
+    uint8_t lvlStart[kListCap + 1];              // first position of level l (entry l + 1 = its end)
+    uint8_t dblCount[kListCap];                  // contacts of level l whose two bodies are both carrying
+    uint8_t sglCount[kListCap];                  // contacts of level l with one carrying body ("solo")
+    uint8_t rank[kListCap];                      // rank of a contact inside its (level, kind)
     uint8_t blvl[kStageMax + 6];                 // next free level of staged body i
     float4 body[1][kStageRecs * 2];              // [stageCap]: records of slot first + i
 };
@@ -773,13 +775,19 @@ __device__ __forceinline__ PairSide pairSide(const SchedEntry e, int side, Stage
 
 // handleContact (xpbd.cpp:405-550 -> handleContactConstraint 321-403), one lane per body.
 // Called by all 32 lanes; `mine` = this lane has a contact side to solve in this round.
-__device__ __forceinline__ void pairContactPositions(const DeviceState &S, int w, const PairSide &P, int side, bool mine)
+// `solo`: the partner body is non-carrying (Static, identity rotation: never moved, zero inverse
+// mass and inertia, previous = pre-solve = current pose), so this lane also evaluates the partner's
+// contact point — by the very expressions the partner's lane would run — and the partner's other
+// terms are exact zeros: generalised inverse mass 0 + dot(ta, 0 * ta), displacement p - p_hat of an
+// unmoved point.
+__device__ __forceinline__ void pairContactPositions(const DeviceState &S, int w, const PairSide &P, int side, bool mine,
+                                                     bool solo, int slotO)
 {
     const Vec3 zero = {0.f, 0.f, 0.f};
     float *row = S.contact + (size_t(w) * kMaxCand + P.c) * kContactWords;
     const uint32_t signBit = side ? 0x80000000u : 0u;
     bool act = mine;
-    Vec3 n = zero, r = zero, x = zero, p = zero;
+    Vec3 n = zero, r = zero, x = zero, p = zero, pSolo = zero;
     Quat q = {1.f, 0.f, 0.f, 0.f};
     Pose prev = {zero, q};
     if (act) {
@@ -797,9 +805,16 @@ __device__ __forceinline__ void pairContactPositions(const DeviceState &S, int w
             const Vec3 contact = side ? avg - n * pen : avg;
             r = rotate(qinv(pre.q), contact - pre.x);
             p = rotate(q, r) + x;
+            if (solo) {
+                const Pose o = loadPose(S, REC_POSE, slotO, w);
+                const Vec3 contactO = side ? avg : avg - n * pen;
+                const Vec3 rO = rotate(qinv(o.q), contactO - o.x);
+                pSolo = rotate(o.q, rO) + o.x;
+            }
         }
     }
-    const Vec3 po = shflXorV(p);
+    Vec3 po = shflXorV(p);
+    if (solo) po = pSolo;
     bool push = false;
     float d = 0.f, wgt = 0.f;
     Vec3 ra = zero;
@@ -813,7 +828,8 @@ __device__ __forceinline__ void pairContactPositions(const DeviceState &S, int w
             wgt = P.inv_m + dot(ta, ra);
         }
     }
-    const float wo = __shfl_xor_sync(kFullMask, wgt, 1);
+    float wo = __shfl_xor_sync(kFullMask, wgt, 1);
+    if (solo) wo = 0.f;
     float lambda_n = 0.f;
     Vec3 e = zero;
     if (push) {
@@ -823,7 +839,8 @@ __device__ __forceinline__ void pairContactPositions(const DeviceState &S, int w
         p = rotate(q, r) + x;
         e = p - p_hat;
     }
-    const Vec3 eo = shflXorV(e);
+    Vec3 eo = shflXorV(e);
+    if (solo) eo = zero;
     bool fric = false;
     float tmag = 0.f, wf = 0.f;
     Vec3 t = zero, fr = zero;
@@ -840,19 +857,22 @@ __device__ __forceinline__ void pairContactPositions(const DeviceState &S, int w
             wf = P.inv_m + dot(fa, fr);
         }
     }
-    const float wfo = __shfl_xor_sync(kFullMask, wf, 1);
+    float wfo = __shfl_xor_sync(kFullMask, wf, 1);
+    if (solo) wfo = 0.f;
     if (fric) {
         const float lambda_t = -tmag / ((side ? wfo : wf) + (side ? wf : wfo) + 0.f);
         if (lambda_t > lambda_n * P.muS) applyPositionalSide(x, q, fr, P.inv_m, t, lambda_t, signBit);
     }
     if (act) {
-        if (side == 0) row[19] = lambda_n;
+        if (side == 0 || solo) row[19] = lambda_n;
         if (P.carrying) putPose(P.rec + 2 * SR_POSE, x, q);
     }
 }
 
 // solveVelocitiesForContact (xpbd.cpp:781-1039), one lane per body; called by all 32 lanes.
-__device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int w, const PairSide &P, int side, bool mine)
+// `solo`: the partner's velocities (current and pre-solve) are zero, so every term it would send is 0
+__device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int w, const PairSide &P, int side, bool mine,
+                                                      bool solo)
 {
     const Vec3 zero = {0.f, 0.f, 0.f};
     const float *row = S.contact + (size_t(w) * kMaxCand + P.c) * kContactWords;
@@ -897,9 +917,10 @@ __device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int 
         }
     }
     {
-        const Vec3 abo = shflXorV(ab);
-        const Vec3 ao = shflXorV(a);
-        const float wo = __shfl_xor_sync(kFullMask, wgt, 1);
+        Vec3 abo = shflXorV(ab);
+        Vec3 ao = shflXorV(a);
+        float wo = __shfl_xor_sync(kFullMask, wgt, 1);
+        if (solo) { abo = zero; ao = zero; wo = 0.f; }
         if (act) {
             // applyRestitutionVelocityUpdate
             const float vnBar = dot(n, side ? abo - ab : ab - abo);
@@ -929,7 +950,8 @@ __device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int 
             const Vec3 rw = rotate(q, r);
             ai = v + cross(o, rw);
         }
-        const Vec3 aio = shflXorV(ai);
+        Vec3 aio = shflXorV(ai);
+        if (solo) aio = zero;
         // applyFrictionVelocityUpdate
         bool go = false;
         float vtLen = 0.f, wi = 0.f;
@@ -948,7 +970,8 @@ __device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int 
                 wi = P.inv_m + dot(fa, fr);
             }
         }
-        const float wio = __shfl_xor_sync(kFullMask, wi, 1);
+        float wio = __shfl_xor_sync(kFullMask, wi, 1);
+        if (solo) wio = 0.f;
         if (go) {
             const float lambda = lambdaN * (c.depth[i] / penSum);
             const float invScale = 1.f / ((side ? wio : wi) + (side ? wi : wio));
@@ -1051,7 +1074,7 @@ __device__ __forceinline__ int fillContactList(const DeviceState &S, int w, Stag
 // is inherently serial (lane 0 of the group; K is ~17), the sort is lane-parallel.
 __device__ __forceinline__ void levelContactList(StagedWorld &sw, int K, int first, int count, int lg)
 {
-    for (int i = lg; i < kListCap; i += kSolveLanes) sw.lvlCount[i] = 0;
+    for (int i = lg; i < kListCap; i += kSolveLanes) { sw.dblCount[i] = 0; sw.sglCount[i] = 0; }
     for (int i = lg; i < count; i += kSolveLanes) sw.blvl[i] = 0;
     __syncwarp();
     if (lg == 0 && K > 0) {
@@ -1062,41 +1085,59 @@ __device__ __forceinline__ void levelContactList(StagedWorld &sw, int K, int fir
             const int ia = int((e.x >> 16) & 0xFF) - first, ib = int(e.x >> 24) - first;     // carrying => staged
             const int la = ca ? sw.blvl[ia] : 0, lb = cb ? sw.blvl[ib] : 0;
             const int lv = max(la, lb);                 // <= k < kListCap
+            const bool solo = ca != cb;                 // the partner is never written: one lane does it all
             sw.list[k].x = (e.x & 0xFFFF00FFu) | (uint32_t(lv) << 8);
-            sw.rank[k] = sw.lvlCount[lv]++;
+            sw.list[k].y = (e.y & 0x7FFFu) | (solo ? 0x8000u : 0u);
+            sw.rank[k] = solo ? sw.sglCount[lv]++ : sw.dblCount[lv]++;
             if (ca) sw.blvl[ia] = uint8_t(lv + 1);
             if (cb) sw.blvl[ib] = uint8_t(lv + 1);
             maxLvl = max(maxLvl, lv);
         }
         int run = 0;
-        for (int l = 0; l <= maxLvl; l++) { const int n = sw.lvlCount[l]; sw.lvlCount[l] = uint8_t(run); run += n; }
+        for (int l = 0; l <= maxLvl; l++) { sw.lvlStart[l] = uint8_t(run); run += sw.dblCount[l] + sw.sglCount[l]; }
+        sw.lvlStart[maxLvl + 1] = uint8_t(run);
     }
     __syncwarp();
-    for (int k = lg; k < K; k += kSolveLanes) sw.order[sw.lvlCount[(sw.list[k].x >> 8) & 0xFF] + sw.rank[k]] = uint8_t(k);
+    for (int k = lg; k < K; k += kSolveLanes) {
+        const SchedEntry e = sw.list[k];
+        const int lv = (e.x >> 8) & 0xFF;
+        sw.order[sw.lvlStart[lv] + ((e.y & 0x8000u) ? sw.dblCount[lv] : 0) + sw.rank[k]] = uint8_t(k);
+    }
     __syncwarp();
 }
 
-// One pass (positions or velocities) over the levelled contacts: the group's four lane pairs take
-// up to four contacts of ONE level at a time; levels in order.  Called by all 32 lanes; a round
-// ends with a warp barrier, which orders the shared-memory body updates of one level before the next.
+// One pass (positions or velocities) over the levelled contacts, one LEVEL at a time, levels in
+// order; inside a level (disjoint carrying bodies, any order) a round hands the group's eight
+// lanes out: a contact between two carrying bodies takes a lane pair (one lane per body), a "solo"
+// contact — the partner is a wall, the ground plane or another Static body with identity rotation,
+// ~95 % of all contacts — takes ONE lane, which supplies the partner's few terms itself.  Called
+// by all 32 lanes; a round ends with a warp barrier, which orders the shared-memory body updates
+// of one level before the next.
 template <bool kVelocities>
 __device__ __forceinline__ void sweepList(const DeviceState &S, int w, StagedWorld &sw, int K, int first, int lg,
                                           const float (*mass)[8])
 {
-    const int pair = lg >> 1, side = lg & 1;
     int i = 0;
     while (__any_sync(kFullMask, i < K)) {
         const bool active = i < K;
-        const int lv = active ? int(sw.list[sw.order[i]].x >> 8) & 0xFF : 0;
-        const int j = i + pair;
-        const SchedEntry ej = sw.list[min(int(sw.order[min(j, kListCap - 1)]), kListCap - 1)];
-        const bool mine = active && j < K && (int(ej.x >> 8) & 0xFF) == lv;
-        const PairSide P = pairSide(mine ? ej : SchedEntry{0u, 0u}, side, sw, first, mass);
-        if (kVelocities) pairContactVelocities(S, w, P, side, mine);
-        else pairContactPositions(S, w, P, side, mine);
-        // the order is sorted by level: the pairs that found work are a prefix of the four
-        const unsigned took = __ballot_sync(kFullMask, mine && side == 0);
-        if (active) i += max(__popc(took & (0xFFu << (threadIdx.x & 24))), 1);
+        int nd = 0, ns = 0;
+        if (active) {
+            const int lv = int(sw.list[sw.order[i]].x >> 8) & 0xFF;
+            const int dblEnd = sw.lvlStart[lv] + sw.dblCount[lv], lvlEnd = sw.lvlStart[lv + 1];
+            nd = min(max(dblEnd - i, 0), kSolveLanes / 2);
+            if (i + nd >= dblEnd) ns = min(lvlEnd - (i + nd), kSolveLanes - 2 * nd);
+        }
+        const bool solo = lg >= 2 * nd;
+        const int j = solo ? i + nd + (lg - 2 * nd) : i + (lg >> 1);
+        const bool mine = solo ? (lg - 2 * nd) < ns : true;
+        const SchedEntry ej = mine ? sw.list[min(int(sw.order[min(j, kListCap - 1)]), kListCap - 1)] : SchedEntry{0u, 0u};
+        // a solo lane works on the carrying body's side
+        const int side = solo ? (((ej.y >> 8) & 1u) ? 0 : 1) : (lg & 1);
+        const PairSide P = pairSide(ej, side, sw, first, mass);
+        const int slotO = int(ej.x >> (16 + 8 * (1 - side))) & 0xFF;
+        if (kVelocities) pairContactVelocities(S, w, P, side, mine, solo);
+        else pairContactPositions(S, w, P, side, mine, solo, slotO);
+        i += nd + ns;
         __syncwarp();
     }
 }
