@@ -119,6 +119,15 @@ __global__ void k_load_checkpoint(DeviceState S)
     S.exCkptCtrl[w] = 1;       // the reference leaves the trigger set (src/sim.cpp:963)
 
     const CkptData &c = *reinterpret_cast<const CkptData *>(S.exCkpt + size_t(w) * kCheckpointBytes);
+    // The checkpoint tensor is user-writable.  The reference only asserts on the agent counts
+    // (src/sim.cpp:1034-1036); counts outside this Manager's team bounds would index past the
+    // world's agent rows, so such a record is refused: the world keeps its state and the refusal
+    // is counted in the overflow counter (hs_overflow_count).
+    if (c.numHiders < 0 || c.numHiders > S.p.maxHiders || c.numSeekers < 0 || c.numSeekers > S.p.maxSeekers ||
+        c.numHiders + c.numSeekers > S.p.agentsPerWorld) {
+        atomicAdd(S.overflow, 1u);
+        return;
+    }
     CkptRegen regen{{c.episodeKey[0], c.episodeKey[1]}, c.numHiders, c.numSeekers};
     regenerateWorld(S, w, &regen);
     WI(S, WF_SCORE0, w) = c.runningScores[0];

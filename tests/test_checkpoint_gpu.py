@@ -89,3 +89,37 @@ def test_save_load_roundtrip_matches_reference():
     run(20)
     check("after load + 20 steps")
     assert sim.overflow_count() == 0
+
+
+def test_load_refuses_out_of_range_agent_counts():
+    """The checkpoint tensor is user-writable: a record whose agent counts exceed the Manager's
+    team bounds (the reference only asserts) must not index past the world's agent rows — the
+    world keeps its state and the refusal is counted."""
+    import gpu_hideseek as gh
+    from compact import hs_dump_compact
+    N = 8
+    sim = gh.HideAndSeekSimulator(num_worlds=N, rand_seed=1, min_hiders=1, max_hiders=2, min_seekers=1, max_seekers=2)
+    sim.init()
+    for _ in range(5):
+        sim.step()
+    for w in range(N):
+        sim.save_checkpoint(w)
+    blob = sim.ckpt_tensor().to_torch()
+    host = blob.cpu().numpy().copy().view(ckpt_dt).reshape(N)
+    host["num_hiders"][2] = 3              # above max_hiders = 2
+    host["num_seekers"][5] = -1
+    host["num_hiders"][6] = 1000000
+    blob.copy_(torch.from_numpy(host.view(np.uint8).reshape(N, 1392)).to(blob.device))
+    for _ in range(3):
+        sim.step()
+    before = hs_dump_compact(sim)
+    sim.ckpt_ctrl_tensor().to_torch().fill_(1)
+    sim.load_checkpoints()
+    after = hs_dump_compact(sim)
+    assert sim.overflow_count() == 3
+    for w in range(N):
+        same = before[w]["pose"].tobytes() == after[w]["pose"].tobytes() and \
+            int(before[w]["cur_episode_step"]) == int(after[w]["cur_episode_step"])
+        assert same == (w in (2, 5, 6)), w          # refused worlds keep their state, the others rewind
+    sim.step()                                      # and the simulator keeps running
+    assert np.isfinite(sim.self_data_tensor().to_torch().cpu().numpy()).all()
