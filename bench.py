@@ -500,7 +500,7 @@ def run_ours(args):
         "config": {"workload": "scripts/benchmark.py semantics: 16000 worlds/GPU x steps, 2 hiders + 2 "
                                "seekers, random move actions every step, renderer off",
                    "worlds_per_gpu": N, "agents_per_world": A, "sharding": f"worlds x{world}",
-                   "l2": "per-GPU state (BVH 208 MB + body records 186 MB + contacts 328 MB + exports 81 MB) exceeds the 126 MB L2",
+                   "l2": "per-GPU state (BVH 208 MB + body records 186 MB + contacts 164 MB + exports 81 MB) exceeds the 126 MB L2",
                    "mean_bodies": E, "mean_candidates": C, "mean_contacts": K,
                    "note": "`value` times exactly --steps steps from a fresh init(); `full_episode` is the "
                            "same metric over one whole 240-step episode (reset wave included)"},

@@ -16,16 +16,33 @@
 
 namespace hs {
 
-struct WorldHull {
+// A hull in world space.  The vertex and plane arrays are indexed by data-dependent ids (half-edge
+// roots, face ids), so a per-thread copy lives in local memory: 1 KB of stack per thread for a
+// pair, whose footprint over a CTA wave exceeds the L1 (11 % of the local loads missed to L2, and
+// every extra lane made it worse).  The arrays therefore live in a shared-memory slot of 51 words
+// per thread (odd stride: lanes reading the same element of their own slots hit 32 banks), and
+// WorldHull is a view of one slot.
+struct HullSlot {
     Vec3 v[kMaxHullVerts];
     Plane p[kMaxHullFaces];
+    Vec3 center;
+};
+static_assert(sizeof(HullSlot) == 51 * 4, "HullSlot stride must stay odd in words");
+
+struct WorldHull {
+    const Vec3 *v;
+    const Plane *p;
     Vec3 center;
     const HullData *h;
 };
 
-__device__ inline void makeWorldHull(WorldHull &W, const HullData &H, Vec3 t, Quat rot, Vec3 scale)
+__device__ __forceinline__ WorldHull viewHull(const HullSlot &slot, const HullData &H)
 {
-    W.h = &H;
+    return {slot.v, slot.p, slot.center, &H};
+}
+
+__device__ inline void makeWorldHull(HullSlot &W, const HullData &H, Vec3 t, Quat rot, Vec3 scale)
+{
     Mat3 r = mat3FromQuat(rot);
     Mat3 vt = {r.c0 * scale.x, r.c1 * scale.y, r.c2 * scale.z};
     Mat3 nt = {r.c0 * (1.f / scale.x), r.c1 * (1.f / scale.y), r.c2 * (1.f / scale.z)};
@@ -81,13 +98,17 @@ __device__ __forceinline__ bool isMinkowskiFace(Vec3 a, Vec3 b, Vec3 c, Vec3 d)
 
 struct EdgeQuery { float sep; Vec3 normal; int edgeA, edgeB; };
 
-__device__ inline EdgeQuery queryEdges(const WorldHull &a, const WorldHull &b)
+// Edges [ea0, ea1) of `a` against every edge of `b`.  The reference's running maximum takes a
+// later pair only when it is strictly larger, so the query over all edges equals the left-biased
+// combination of the queries over consecutive ranges (combineEdgeQueries); a positive separation
+// ends the reference's loop, and then only its sign is used (doSAT, narrowphase.cpp:659-739).
+__device__ inline EdgeQuery queryEdgeRange(const WorldHull &a, const WorldHull &b, int ea0, int ea1)
 {
     EdgeQuery q;
     q.sep = -FLT_MAX; q.normal = {0.f, 0.f, 0.f}; q.edgeA = 0; q.edgeB = 0;
     const HullData &A = *a.h, &B = *b.h;
-    const int na = A.numHedges / 2, nb = B.numHedges / 2;
-    for (int ea = 0; ea < na; ea++) {
+    const int nb = B.numHedges / 2;
+    for (int ea = ea0; ea < ea1; ea++) {
         int ha = ea * 2;
         Vec3 aN1 = a.p[A.hedgeFace[ha]].n, aN2 = a.p[A.hedgeFace[ha + 1]].n;
         Vec3 a1 = a.v[A.hedgeRoot[ha]], a2 = a.v[A.hedgeRoot[A.hedgeNext[ha]]];
@@ -120,6 +141,16 @@ __device__ inline EdgeQuery queryEdges(const WorldHull &a, const WorldHull &b)
         }
     }
     return q;
+}
+
+__device__ inline EdgeQuery queryEdges(const WorldHull &a, const WorldHull &b)
+{
+    return queryEdgeRange(a, b, 0, a.h->numHedges / 2);
+}
+
+__device__ __forceinline__ EdgeQuery combineEdgeQueries(const EdgeQuery &first, const EdgeQuery &second)
+{
+    return second.sep > first.sep ? second : first;
 }
 
 __device__ __forceinline__ int findIncidentFace(const WorldHull &h, Vec3 refNormal)
@@ -326,14 +357,25 @@ __device__ inline Manifold edgeContact(const EdgeQuery &q, const WorldHull &a, c
 //           warp runs one code path at a time.
 // Each pair still writes the contact slot of its own candidate index, so the solver sees
 // contacts in the reference's creation order no matter which lane produced them.
-constexpr int kNpWorlds = 16;
-constexpr int kNpThreads = 128;
+#ifndef HS_NP_WORLDS
+#define HS_NP_WORLDS 32
+#endif
+#ifndef HS_NP_THREADS
+#define HS_NP_THREADS 384
+#endif
+#ifndef HS_NP_MINB
+#define HS_NP_MINB 2
+#endif
+constexpr int kNpWorlds = HS_NP_WORLDS;
+constexpr int kNpThreads = HS_NP_THREADS;
 constexpr int kNpListCap = kNpWorlds * kMaxCand;
+static_assert(kNpWorlds <= 32 && kNpThreads % kNpWorlds == 0 && kNpThreads % 32 == 0, "narrowphase CTA shape");
 
 struct NpSmem {
     AssetTable assets;
     uint32_t list[kNpListCap];      // plane pairs grow from the front, hull pairs from the back
     int numPlane, numHull;
+    HullSlot hull[kNpThreads];      // one world-space hull per thread (see HullSlot)
 };
 
 __device__ __forceinline__ AABB objAABBOf(const AssetTable &AT, int obj)
@@ -354,7 +396,7 @@ __device__ __forceinline__ void writeContact(const DeviceState &S, int w, int c,
     S.cmeta[size_t(w) * kMaxCand + c] = uint32_t(ref) | (uint32_t(alt) << 8) | (uint32_t(m.n) << 16);
 }
 
-__global__ void __launch_bounds__(kNpThreads, 7) k_narrowphase(DeviceState S)
+__global__ void __launch_bounds__(kNpThreads, HS_NP_MINB) k_narrowphase(DeviceState S)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     NpSmem &sm = *reinterpret_cast<NpSmem *>(smemRaw);
@@ -394,7 +436,7 @@ __global__ void __launch_bounds__(kNpThreads, 7) k_narrowphase(DeviceState S)
                 S.cmeta[size_t(w) * kMaxCand + c] = 0;
                 continue;
             }
-            uint32_t rec = uint32_t(wi) | (uint32_t(c) << 4) | (uint32_t(a) << 12) | (uint32_t(b) << 20);
+            uint32_t rec = uint32_t(wi) | (uint32_t(c) << 5) | (uint32_t(a) << 13) | (uint32_t(b) << 21);
             if (plane) sm.list[atomicAdd(&sm.numPlane, 1)] = rec;
             else sm.list[kNpListCap - 1 - atomicAdd(&sm.numHull, 1)] = rec;
         }
@@ -405,10 +447,11 @@ __global__ void __launch_bounds__(kNpThreads, 7) k_narrowphase(DeviceState S)
     const int numPlane = sm.numPlane, numHull = sm.numHull;
     for (int i = tid; i < numPlane; i += kNpThreads) {
         const uint32_t rec = sm.list[i];
-        const int w = w0 + int(rec & 15), c = int(rec >> 4) & 0xFF, a = int(rec >> 12) & 0xFF, b = int(rec >> 20) & 0xFF;
-        WorldHull ha;
+        const int w = w0 + int(rec & 31), c = int(rec >> 5) & 0xFF, a = int(rec >> 13) & 0xFF, b = int(rec >> 21) & 0xFF;
         const Pose pa = loadPose(S, REC_POSE, a, w), pb = loadPose(S, REC_POSE, b, w);
-        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], pa.x, pa.q, loadScale(S, a, w));
+        const HullData &HA = AT.hull[metaObj(META(S, a, w))];
+        makeWorldHull(sm.hull[tid], HA, pa.x, pa.q, loadScale(S, a, w));
+        const WorldHull ha = viewHull(sm.hull[tid], HA);
         Vec3 n = rotate(pb.q, v3(0, 0, 1));
         Plane pl = {n, dot(n, pb.x)};
         bool has = false;
@@ -422,24 +465,65 @@ __global__ void __launch_bounds__(kNpThreads, 7) k_narrowphase(DeviceState S)
         else S.cmeta[size_t(w) * kMaxCand + c] = 0;
     }
 
-    // ---- pass 2b: hull vs hull -----------------------------------------------------------------------
-    for (int i = tid; i < numHull; i += kNpThreads) {
-        const uint32_t rec = sm.list[kNpListCap - 1 - i];
-        const int w = w0 + int(rec & 15), c = int(rec >> 4) & 0xFF, a = int(rec >> 12) & 0xFF, b = int(rec >> 20) & 0xFF;
-        WorldHull ha, hb;
-        const Pose pa = loadPose(S, REC_POSE, a, w), pb = loadPose(S, REC_POSE, b, w);
-        makeWorldHull(ha, AT.hull[metaObj(META(S, a, w))], pa.x, pa.q, loadScale(S, a, w));
-        makeWorldHull(hb, AT.hull[metaObj(META(S, b, w))], pb.x, pb.q, loadScale(S, b, w));
+    // ---- pass 2b: hull vs hull, two lanes per pair --------------------------------------------------
+    // The SAT of one pair is a long serial chain (two face queries, then up to 12 x 12 edge pairs)
+    // and a launch holds only ~5 such pairs per world, so the pass is bound by that chain, not by
+    // issue slots.  Lanes 2k / 2k+1 share pair k: lane 0 runs queryFaces(A, B) and the first half
+    // of A's edges, lane 1 queryFaces(B, A) and the second half; the halves are exchanged with
+    // full-mask shuffles between warp-uniform phases and combined in the reference's order
+    // (combineEdgeQueries), so the contact is bit-identical to the one-lane pass.  Lane 0 then
+    // builds and writes the manifold.  Each lane also transforms only one of the two hulls.
+    const int hullLanes = numHull * 2;
+    for (int it = tid; (it & ~31) < hullLanes; it += kNpThreads) {
+        const bool valid = it < hullLanes;
+        const int half = it & 1;
+        const uint32_t rec = sm.list[kNpListCap - 1 - (valid ? it >> 1 : 0)];
+        const int w = w0 + int(rec & 31), c = int(rec >> 5) & 0xFF, a = int(rec >> 13) & 0xFF, b = int(rec >> 21) & 0xFF;
+        // each lane transforms ONE of the two hulls into its slot; the pair reads both
+        const HullData &HA = AT.hull[metaObj(META(S, a, w))], &HB = AT.hull[metaObj(META(S, b, w))];
+        __syncwarp();                                       // the slots' previous readers are done
+        {
+            const int body = half ? b : a;
+            const Pose ps = loadPose(S, REC_POSE, body, w);
+            makeWorldHull(sm.hull[tid], half ? HB : HA, ps.x, ps.q, loadScale(S, body, w));
+        }
+        __syncwarp();
+        const WorldHull ha = viewHull(sm.hull[tid & ~1], HA), hb = viewHull(sm.hull[tid | 1], HB);
+
+        FaceQuery mine = half ? queryFaces(hb, ha) : queryFaces(ha, hb);
+        __syncwarp();
+        FaceQuery other;
+        other.sep = __shfl_xor_sync(0xFFFFFFFFu, mine.sep, 1);
+        other.face = __shfl_xor_sync(0xFFFFFFFFu, mine.face, 1);
+        other.plane.n.x = __shfl_xor_sync(0xFFFFFFFFu, mine.plane.n.x, 1);
+        other.plane.n.y = __shfl_xor_sync(0xFFFFFFFFu, mine.plane.n.y, 1);
+        other.plane.n.z = __shfl_xor_sync(0xFFFFFFFFu, mine.plane.n.z, 1);
+        other.plane.d = __shfl_xor_sync(0xFFFFFFFFu, mine.plane.d, 1);
+        const FaceQuery fa = half ? other : mine, fb = half ? mine : other;
+        bool separated = fa.sep > 0.0f || fb.sep > 0.0f;
+
+        EdgeQuery em;
+        em.sep = -FLT_MAX; em.normal = {0.f, 0.f, 0.f}; em.edgeA = 0; em.edgeB = 0;
+        if (!separated) {
+            const int na = ha.h->numHedges / 2, mid = na / 2;
+            em = queryEdgeRange(ha, hb, half ? mid : 0, half ? na : mid);
+        }
+        __syncwarp();
+        EdgeQuery eo;
+        eo.sep = __shfl_xor_sync(0xFFFFFFFFu, em.sep, 1);
+        eo.normal.x = __shfl_xor_sync(0xFFFFFFFFu, em.normal.x, 1);
+        eo.normal.y = __shfl_xor_sync(0xFFFFFFFFu, em.normal.y, 1);
+        eo.normal.z = __shfl_xor_sync(0xFFFFFFFFu, em.normal.z, 1);
+        eo.edgeA = __shfl_xor_sync(0xFFFFFFFFu, em.edgeA, 1);
+        eo.edgeB = __shfl_xor_sync(0xFFFFFFFFu, em.edgeB, 1);
+        if (half || !valid) continue;
+        const EdgeQuery eq = combineEdgeQueries(em, eo);
+
         bool has = false;
         int ref = a, alt = b;
         Manifold m;
         do {
-            FaceQuery fa = queryFaces(ha, hb);
-            if (fa.sep > 0.0f) break;
-            FaceQuery fb = queryFaces(hb, ha);
-            if (fb.sep > 0.0f) break;
-            EdgeQuery eq = queryEdges(ha, hb);
-            if (eq.sep > 0.0f) break;
+            if (separated || eq.sep > 0.0f) break;
             bool faceA = fa.sep > eq.sep, faceB = fb.sep > eq.sep;
             if (faceA || faceB) {
                 bool aIsRef = fa.sep >= fb.sep;

@@ -187,6 +187,7 @@ static int createBody(hs_sim *sim, const hs_config *cfg, int A)
         HS_CUDA(cudaFuncSetAttribute(k_rays<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
         HS_CUDA(cudaFuncSetAttribute(k_rays<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
         HS_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, solveSmemBytes(kStageMax)));
+        HS_CUDA(cudaFuncSetAttribute(k_narrowphase, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NpSmem)));
         if (const char *e = getenv("HIDESEEK_RAY_ORDER")) sim->raysNearestFirst = strcmp(e, "reference") != 0;
     }
     HS_CUDA(cudaStreamCreateWithFlags(&sim->graphStream, cudaStreamNonBlocking));

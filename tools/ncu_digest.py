@@ -44,5 +44,11 @@ if len(sys.argv) > 3 and sys.argv[2] == '--traffic':
     for r in rows[2:]:
         name = r[ki].split('(')[0].replace('void ', '').split('<')[0].replace('hs::', '')
         acc[name].append(float(r[ir].replace(',', '')) * mult[units[ir]] + float(r[iw].replace(',', '')) * mult[units[iw]])
-    out = {'source': sys.argv[3], 'kernels': {k: scale * sum(v) / len(v) for k, v in acc.items()}}
+    # kernels not in this capture (k_agent_views has its own report) keep their previous entry
+    try:
+        out = json.load(open('profiles/traffic.json'))
+    except (OSError, ValueError):
+        out = {'kernels': {}}
+    out['source'] = sys.argv[3]
+    out['kernels'].update({k: scale * sum(v) / len(v) for k, v in acc.items()})
     json.dump(out, open('profiles/traffic.json', 'w'), indent=1)
