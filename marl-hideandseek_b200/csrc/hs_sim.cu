@@ -557,12 +557,25 @@ static bool stagedSolveDefault()
     return !(e && strcmp(e, "global") == 0);
 }
 
+// HIDESEEK_HEAD_REFIT=1 runs the BVH update at the head of a step like the reference's task graph
+// does (src/sim.cpp:1307-1313 -> setupBroadphaseTasks).  It is skipped by default because it cannot
+// change anything: every path that moves a body or its velocity outside a step (hs_init, checkpoint
+// loads) and the step itself end with a BVH update of the worlds they touched, movementSystem only
+// writes forces, leaf boxes are a pure function of pose / velocity / scale and the refit only grows
+// bounds that already contain those boxes (tests/test_head_refit_gpu.py: bit-identical BVH).
+static bool headRefitDefault()
+{
+    const char *e = getenv("HIDESEEK_HEAD_REFIT");
+    return e && e[0] == '1';
+}
+
 struct Launcher {
     DeviceState S;
     cudaStream_t st;
     int count = 0;
     bool fusedSolve = fusedSolveDefault();
     bool stagedSolve = stagedSolveDefault();
+    bool headRefit = headRefitDefault();
     // graph capture only: side streams + events for the independent observation-stage kernels
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t auxFork = nullptr, auxJoin[2] = {nullptr, nullptr};
@@ -641,7 +654,7 @@ void launchReset(Launcher &L)
 void launchStep(Launcher &L, float cosThr, bool nearestFirst)
 {
     k_move<<<L.gAgent(), 128, 0, L.st>>>(L.S); L.mark("k_move");
-    launchBroadphaseSetup(L, false);       // a rebuild is only ever pending right after a reset
+    if (L.headRefit) launchBroadphaseSetup(L, false);       // a rebuild is only ever pending right after a reset
     {
         const unsigned nb = unsigned((L.N() + kActWarps * (32 / kActLanes) - 1) / (kActWarps * (32 / kActLanes)));
         if (nearestFirst) k_action<true><<<nb, kActWarps * 32, 0, L.st>>>(L.S);

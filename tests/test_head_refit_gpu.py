@@ -1,0 +1,70 @@
+"""The BVH update at the head of a step (setupBroadphaseTasks at the start of the reference's Step
+graph, src/sim.cpp:1307-1313) is skipped by default: the previous step (or init / a checkpoint
+load) ended with the same update on the same poses and velocities, so it cannot change a leaf box
+or grow a node.  HIDESEEK_HEAD_REFIT=1 restores the launch; the two must agree bit for bit on the
+whole world record — BVH nodes and leaves, candidate pairs, contacts, poses — over an episode, its
+reset wave, forced resets and a checkpoint round trip."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from compact import hs_dump_compact, hs_set_debug
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(head_refit, N=384, steps=250):
+    import gpu_hideseek as gh
+    if head_refit:
+        os.environ["HIDESEEK_HEAD_REFIT"] = "1"
+    else:
+        os.environ.pop("HIDESEEK_HEAD_REFIT", None)
+    try:
+        sim = gh.HideAndSeekSimulator(num_worlds=N, rand_seed=11, min_hiders=1, max_hiders=3,
+                                      min_seekers=1, max_seekers=3)
+        A = 6
+        sim.init()
+        hs_set_debug(sim, 1)
+        launches = None
+        act = sim.action_tensor().to_torch()
+        gen = torch.Generator(device="cpu").manual_seed(5)
+        dumps = []
+        for step in range(steps):
+            a = torch.zeros((N * A, 5), dtype=torch.int32)
+            a[:, 0:3] = torch.randint(0, 11, (N * A, 3), generator=gen, dtype=torch.int32)
+            a[:, 3] = (torch.rand(N * A, generator=gen) < 0.3).int()
+            a[:, 4] = (torch.rand(N * A, generator=gen) < 0.15).int()
+            act.copy_(a.to(act.device))
+            if step == 60:
+                sim.trigger_reset(7, 1)
+            if step == 100:
+                for w in (3, 200):
+                    sim.save_checkpoint(w)
+            if step == 130:
+                for w in (3, 200):
+                    sim.load_checkpoint(w)
+            sim.step()
+            if launches is None:
+                launches = sim.last_step_launches()
+            if step % 20 == 0 or step in (61, 131, 239, 240, 241):
+                dumps.append((step, hs_dump_compact(sim).tobytes()))
+        assert sim.overflow_count() == 0
+        return launches, dumps
+    finally:
+        os.environ.pop("HIDESEEK_HEAD_REFIT", None)
+
+
+def test_head_of_step_bvh_update_changes_nothing():
+    l1, with_refit = _run(True)
+    l0, without = _run(False)
+    assert l1 > l0, (l1, l0)                     # the default really launches less
+    assert len(with_refit) == len(without)
+    for (s1, a), (s0, b) in zip(with_refit, without):
+        assert s1 == s0
+        if a != b:
+            ra = np.frombuffer(a, dtype=np.uint8).reshape(384, -1)
+            rb = np.frombuffer(b, dtype=np.uint8).reshape(384, -1)
+            bad = np.nonzero((ra != rb).any(axis=1))[0]
+            raise AssertionError(f"step {s1}: {len(bad)} worlds differ, first {bad[:5]}")
