@@ -25,12 +25,14 @@ def sass_lineinfo(obj, kernel):
     subprocess.check_call(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=tmp, stdout=subprocess.DEVNULL)
     cubins = [os.path.join(tmp, f) for f in os.listdir(tmp) if f.endswith(".cubin")]
     out = subprocess.run(["nvdisasm", "-gi", "-c"] + cubins, capture_output=True, text=True).stdout
+    # "7k_solve" must not match "17k_solve_positions" or "14k_solve_global": anchor both ends
+    pat = re.compile(r"(?<![0-9])" + re.escape(kernel) + (r"(?=[EI])" if kernel[-1].isalnum() and "IL" not in kernel else ""))
     frames, cur, infn, table = [], [], False, {}
     for line in out.splitlines():
         if line.startswith(".text."):
-            infn = kernel in line
+            infn = pat.search(line) is not None
             continue
-        if line.lstrip().startswith("//---") and infn and ".text." in line and kernel not in line:
+        if line.lstrip().startswith("//---") and infn and ".text." in line and not pat.search(line):
             infn = False
         if not infn:
             continue
