@@ -562,7 +562,14 @@ static bool stagedSolveDefault()
 // change anything: every path that moves a body or its velocity outside a step (hs_init, checkpoint
 // loads) and the step itself end with a BVH update of the worlds they touched, movementSystem only
 // writes forces, leaf boxes are a pure function of pose / velocity / scale and the refit only grows
-// bounds that already contain those boxes (tests/test_head_refit_gpu.py: bit-identical BVH).
+// bounds that already contain those boxes (tests/test_step_variants_gpu.py: bit-identical BVH).
+// HIDESEEK_FUSED_SUBSTEP=0 launches k_substep in front of every substep; by default only the first
+// substep of a step does, the staged k_solve integrates the next substep's bodies at its tail.
+static bool fusedSubstepDefault()
+{
+    const char *e = getenv("HIDESEEK_FUSED_SUBSTEP");
+    return !(e && e[0] == '0');
+}
 static bool headRefitDefault()
 {
     const char *e = getenv("HIDESEEK_HEAD_REFIT");
@@ -576,6 +583,7 @@ struct Launcher {
     bool fusedSolve = fusedSolveDefault();
     bool stagedSolve = stagedSolveDefault();
     bool headRefit = headRefitDefault();
+    bool fusedSubstep = fusedSubstepDefault();
     // graph capture only: side streams + events for the independent observation-stage kernels
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t auxFork = nullptr, auxJoin[2] = {nullptr, nullptr};
@@ -662,13 +670,15 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
         L.mark("k_action");
     }
     k_broadphase<<<(L.N() + kBroadWarps - 1) / kBroadWarps, kBroadWarps * 32, 0, L.st>>>(L.S); L.mark("k_broadphase");
+    const bool tailSubstep = L.fusedSolve && L.stagedSolve && L.fusedSubstep;
     for (int i = 0; i < kSubsteps; i++) {
-        k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep");
+        if (i == 0 || !tailSubstep) { k_substep<<<L.gBody(), 256, 0, L.st>>>(L.S); L.mark("k_substep"); }
         k_narrowphase<<<(L.N() + kNpWorlds - 1) / kNpWorlds, kNpThreads, sizeof(NpSmem), L.st>>>(L.S); L.mark("k_narrowphase");
         if (L.fusedSolve && L.stagedSolve) {
             // body area of the staged solver: 9 boxes + 2 ramps + ground plane + this Manager's agent slots
             const int stageCap = kMaxBoxes + kMaxRamps + 1 + L.S.p.agentsPerWorld;
-            k_solve<<<(L.N() + kStagedGroups - 1) / kStagedGroups, kStagedThreads, solveSmemBytes(stageCap), L.st>>>(L.S, stageCap);
+            k_solve<<<(L.N() + kStagedGroups - 1) / kStagedGroups, kStagedThreads, solveSmemBytes(stageCap), L.st>>>(
+                L.S, stageCap, tailSubstep && i + 1 < kSubsteps ? 1 : 0);
             L.mark("k_solve");
         } else if (L.fusedSolve) {
             k_solve_global<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_global");

@@ -19,31 +19,12 @@ namespace hs {
 
 __device__ __forceinline__ float substepH() { return kDeltaT / float(kSubsteps); }
 
-// one thread per (slot, world)
-__global__ void k_substep(DeviceState S)
+// substepRigidBodies for one non-static body (xpbd.cpp:100-185): pose and velocity after the
+// explicit integration step.  `vel` is the body's velocity record, `ft` its force / torque record.
+__device__ __forceinline__ void integrateBody(uint32_t m, Vec3 &x, Quat &q, const Vel6 &vel, const Vel6 &ft, Vec3 &v, Vec3 &omega)
 {
-    const int N = S.p.numWorlds;
-    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)kMaxBodies * N) return;
-    int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
-    if (s >= WI(S, WF_NUM_BODIES, w)) return;
-
-    uint32_t m = META(S, s, w);
-    Pose cur = loadPose(S, REC_POSE, s, w);
-    Vec3 x = cur.x;
-    Quat q = cur.q;
-    storePose(S, REC_PREV, s, w, x, q);
-
-    if (metaResp(m) == RESP_STATIC) {
-        storePose(S, REC_PRE, s, w, x, q);
-        storeVel6(S, REC_PREVEL, s, w, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f});
-        return;
-    }
-
-    Vel6 vel = loadVel6(S, REC_VEL, s, w);
-    Vel6 ft = loadVel6(S, REC_FORCE, s, w);
-    Vec3 v = vel.v;
-    Vec3 omega = vel.w;
+    v = vel.v;
+    omega = vel.w;
     const ObjectData &O = c_assets.obj[metaObj(m)];
     float inv_m = O.invMass;
     Vec3 inv_I = {O.invInertia[0], O.invInertia[1], O.invInertia[2]};
@@ -69,10 +50,40 @@ __global__ void k_substep(DeviceState S)
     Quat applyOmega = fromAngularVec((0.5f * h) * omega);
     q = q + applyOmega * q;
     q = qnormalize(q);
+}
+
+// one body of one world, state in HBM
+__device__ __forceinline__ void substepBody(const DeviceState &S, int s, int w)
+{
+    uint32_t m = META(S, s, w);
+    Pose cur = loadPose(S, REC_POSE, s, w);
+    Vec3 x = cur.x;
+    Quat q = cur.q;
+    storePose(S, REC_PREV, s, w, x, q);
+
+    if (metaResp(m) == RESP_STATIC) {
+        storePose(S, REC_PRE, s, w, x, q);
+        storeVel6(S, REC_PREVEL, s, w, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f});
+        return;
+    }
+
+    Vec3 v, omega;
+    integrateBody(m, x, q, loadVel6(S, REC_VEL, s, w), loadVel6(S, REC_FORCE, s, w), v, omega);
 
     storePose(S, REC_POSE, s, w, x, q);
     storePose(S, REC_PRE, s, w, x, q);
     storeVel6(S, REC_PREVEL, s, w, v, omega);
+}
+
+// one thread per (slot, world)
+__global__ void k_substep(DeviceState S)
+{
+    const int N = S.p.numWorlds;
+    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)kMaxBodies * N) return;
+    int s = int(idx % kMaxBodies), w = int(idx / kMaxBodies);
+    if (s >= WI(S, WF_NUM_BODIES, w)) return;
+    substepBody(S, s, w);
 }
 
 struct MassData { float inv_m; Vec3 inv_I; float muS, muD; };
@@ -1142,7 +1153,7 @@ __device__ __forceinline__ void sweepList(const DeviceState &S, int w, StagedWor
     }
 }
 
-__global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceState S, int stageCap)
+__global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceState S, int stageCap, int integrateNext)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     float (*mass)[8] = reinterpret_cast<float (*)[8]>(smemRaw);
@@ -1177,6 +1188,10 @@ __global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceS
     if (live && !work) {                      // staging range too long (never in generated levels)
         const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
         solveWorldGlobal(S, w, *reinterpret_cast<SolveGroupSmem *>(&sw), lg, gmask, gshift);
+        if (integrateNext) {
+            __syncwarp(gmask);
+            for (int s = lg, nb = WI(S, WF_NUM_BODIES, w); s < nb; s += kSolveLanes) substepBody(S, s, w);
+        }
     }
     __syncwarp();
 
@@ -1206,6 +1221,10 @@ __global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceS
     if (tooMany) {
         const unsigned gmask = ((1u << kSolveLanes) - 1u) << gshift;
         solveWorldGlobal(S, w, *reinterpret_cast<SolveGroupSmem *>(&sw), lg, gmask, gshift);
+        if (integrateNext) {
+            __syncwarp(gmask);
+            for (int s = lg, nb = WI(S, WF_NUM_BODIES, w); s < nb; s += kSolveLanes) substepBody(S, s, w);
+        }
     }
     __syncwarp();
     const bool staged = work && !tooMany;
@@ -1247,14 +1266,44 @@ __global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceS
     // ---- velocity pass ----------------------------------------------------------------------------
     sweepList<true>(S, w, sw, K, first, lg, mass);
     // ---- pose + velocity back to HBM ----------------------------------------------------------------
-    if (staged) {
+    if (staged && !integrateNext) {
         for (int i = lg; i < count * 4; i += kSolveLanes) {
             const int j = i >> 2, q = i & 3;             // two float4 of POSE, then two of VEL
             float4 *dst = recPtr(S, q < 2 ? REC_POSE : REC_VEL, first + j, w);
             dst[q & 1] = sw.body[j][q < 2 ? 2 * SR_POSE + q : 2 * SR_VEL + (q - 2)];
         }
-        if (lg == 0) WI(S, WF_NUM_CONTACTS, w) = total;
     }
+    // ---- ... or, when another substep follows, its substepRigidBodies right here ------------------------
+    // The next substep starts by integrating every body (k_substep).  For the staged bodies pose and
+    // velocity are in shared memory at this point, so the integration runs on them and all five
+    // records go out once.  Bodies outside the staged range are Static with identity rotation: no
+    // solver writes them, so the PREV / PRE / PREVEL records the step's first k_substep gave them
+    // are still what this substep's would write.
+    if (staged && integrateNext) {
+        __syncwarp();
+        for (int j = lg; j < count; j += kSolveLanes) {
+            const int s = first + j;
+            const uint32_t m = META(S, s, w);
+            const Pose cur = poseOf(sw.body[j] + 2 * SR_POSE);
+            const Vel6 vel = vel6Of(sw.body[j] + 2 * SR_VEL);
+            Vec3 x = cur.x;
+            Quat q = cur.q;
+            storePose(S, REC_PREV, s, w, x, q);
+            storeVel6(S, REC_VEL, s, w, vel.v, vel.w);
+            if (metaResp(m) == RESP_STATIC) {
+                storePose(S, REC_POSE, s, w, x, q);
+                storePose(S, REC_PRE, s, w, x, q);
+                storeVel6(S, REC_PREVEL, s, w, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f});
+            } else {
+                Vec3 v, omega;
+                integrateBody(m, x, q, vel, loadVel6(S, REC_FORCE, s, w), v, omega);
+                storePose(S, REC_POSE, s, w, x, q);
+                storePose(S, REC_PRE, s, w, x, q);
+                storeVel6(S, REC_PREVEL, s, w, v, omega);
+            }
+        }
+    }
+    if (staged && lg == 0) WI(S, WF_NUM_CONTACTS, w) = total;
 }
 
 }  // namespace hs

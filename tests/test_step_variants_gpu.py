@@ -3,7 +3,8 @@ graph, src/sim.cpp:1307-1313) is skipped by default: the previous step (or init 
 load) ended with the same update on the same poses and velocities, so it cannot change a leaf box
 or grow a node.  HIDESEEK_HEAD_REFIT=1 restores the launch; the two must agree bit for bit on the
 whole world record — BVH nodes and leaves, candidate pairs, contacts, poses — over an episode, its
-reset wave, forced resets and a checkpoint round trip."""
+reset wave, forced resets and a checkpoint round trip.  Same harness for the other launch the step
+graph drops: k_substep of substeps 2-4 (done at the tail of k_solve)."""
 import os
 
 import numpy as np
@@ -15,12 +16,14 @@ from compact import hs_dump_compact, hs_set_debug
 pytestmark = pytest.mark.gpu
 
 
-def _run(head_refit, N=384, steps=250):
+KNOBS = ("HIDESEEK_HEAD_REFIT", "HIDESEEK_FUSED_SUBSTEP")
+
+
+def _run(env, N=384, steps=250):
     import gpu_hideseek as gh
-    if head_refit:
-        os.environ["HIDESEEK_HEAD_REFIT"] = "1"
-    else:
-        os.environ.pop("HIDESEEK_HEAD_REFIT", None)
+    for k in KNOBS:
+        os.environ.pop(k, None)
+    os.environ.update(env)
     try:
         sim = gh.HideAndSeekSimulator(num_worlds=N, rand_seed=11, min_hiders=1, max_hiders=3,
                                       min_seekers=1, max_seekers=3)
@@ -53,18 +56,33 @@ def _run(head_refit, N=384, steps=250):
         assert sim.overflow_count() == 0
         return launches, dumps
     finally:
-        os.environ.pop("HIDESEEK_HEAD_REFIT", None)
+        for k in KNOBS:
+            os.environ.pop(k, None)
 
 
-def test_head_of_step_bvh_update_changes_nothing():
-    l1, with_refit = _run(True)
-    l0, without = _run(False)
-    assert l1 > l0, (l1, l0)                     # the default really launches less
-    assert len(with_refit) == len(without)
-    for (s1, a), (s0, b) in zip(with_refit, without):
+def _same(with_launch, without):
+    assert len(with_launch) == len(without)
+    for (s1, a), (s0, b) in zip(with_launch, without):
         assert s1 == s0
         if a != b:
             ra = np.frombuffer(a, dtype=np.uint8).reshape(384, -1)
             rb = np.frombuffer(b, dtype=np.uint8).reshape(384, -1)
             bad = np.nonzero((ra != rb).any(axis=1))[0]
             raise AssertionError(f"step {s1}: {len(bad)} worlds differ, first {bad[:5]}")
+
+
+def test_head_of_step_bvh_update_changes_nothing():
+    l1, with_refit = _run({"HIDESEEK_HEAD_REFIT": "1"})
+    l0, without = _run({})
+    assert l1 > l0, (l1, l0)                     # the default really launches less
+    _same(with_refit, without)
+
+
+def test_substep_at_the_tail_of_the_solver_is_the_substep_kernel():
+    """Substeps 2-4 of a step are integrated on the staged bodies at the tail of k_solve instead of
+    by a k_substep launch (HIDESEEK_FUSED_SUBSTEP=0 launches it): same arithmetic on the same values,
+    so the whole world record must be bit-identical."""
+    l1, launched = _run({"HIDESEEK_FUSED_SUBSTEP": "0"})
+    l0, fused = _run({})
+    assert l1 > l0 and (l1 - l0) % 3 == 0, (l1, l0)          # three launches per world slice
+    _same(launched, fused)
