@@ -27,7 +27,10 @@ namespace hs {
 #define HS_VOTE_NUM 1
 #define HS_VOTE_DEN 1
 #endif
-constexpr int kRayThreads = 160;
+#ifndef HS_RAY_THREADS
+#define HS_RAY_THREADS 160
+#endif
+constexpr int kRayThreads = HS_RAY_THREADS;
 constexpr int kMaxVisRays = kMaxAgents * (kMaxBoxes + kMaxRamps + kMaxAgents - 1);   // 96
 constexpr int kMaxRays = kMaxAgents * 30 + kMaxVisRays;                               // 276 per world
 constexpr int kRayQueueA = 1024, kRayQueueB = 384;
