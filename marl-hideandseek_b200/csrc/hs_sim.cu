@@ -134,6 +134,8 @@ static int createBody(hs_sim *sim, const hs_config *cfg, int A)
     HS_TRY(devAlloc(sim, &S.dfsLeaf, size_t(kDfsStride) * N));
     HS_TRY(devAlloc(sim, &S.resetList, N));
     HS_TRY(devAlloc(sim, &S.resetCount, N));
+    HS_TRY(devAlloc(sim, &S.solveOrder, size_t(kSolveOrderBufs) * kSolveOrderBuckets * N));
+    HS_TRY(devAlloc(sim, &S.solveCnt, N + 64));
     HS_TRY(devAlloc(sim, &S.cand, size_t(kMaxCand) * N));
     HS_TRY(devAlloc(sim, &S.contact, size_t(kMaxCand) * kContactWords * N));
     HS_TRY(devAlloc(sim, &S.cmeta, size_t(kMaxCand) * N));
@@ -570,6 +572,13 @@ static bool fusedSubstepDefault()
     const char *e = getenv("HIDESEEK_FUSED_SUBSTEP");
     return !(e && e[0] == '0');
 }
+// HIDESEEK_SOLVE_ORDER=0: k_solve takes its worlds in index order instead of grouping worlds whose
+// contact sweeps need the same number of rounds (same results either way).
+static bool orderedSolveDefault()
+{
+    const char *e = getenv("HIDESEEK_SOLVE_ORDER");
+    return !(e && e[0] == '0');
+}
 static bool headRefitDefault()
 {
     const char *e = getenv("HIDESEEK_HEAD_REFIT");
@@ -584,6 +593,7 @@ struct Launcher {
     bool stagedSolve = stagedSolveDefault();
     bool headRefit = headRefitDefault();
     bool fusedSubstep = fusedSubstepDefault();
+    bool orderedSolve = false;          // set by the step-graph capture only (fixed slices): see k_solve
     // graph capture only: side streams + events for the independent observation-stage kernels
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t auxFork = nullptr, auxJoin[2] = {nullptr, nullptr};
@@ -678,7 +688,7 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
             // body area of the staged solver: 9 boxes + 2 ramps + ground plane + this Manager's agent slots
             const int stageCap = kMaxBoxes + kMaxRamps + 1 + L.S.p.agentsPerWorld;
             k_solve<<<(L.N() + kStagedGroups - 1) / kStagedGroups, kStagedThreads, solveSmemBytes(stageCap), L.st>>>(
-                L.S, stageCap, tailSubstep && i + 1 < kSubsteps ? 1 : 0);
+                L.S, stageCap, tailSubstep && i + 1 < kSubsteps ? 1 : 0, L.orderedSolve ? i % kSolveOrderBufs : -1);
             L.mark("k_solve");
         } else if (L.fusedSolve) {
             k_solve_global<<<(L.N() + kSolveGroups - 1) / kSolveGroups, kSolveThreads, 0, L.st>>>(L.S); L.mark("k_solve_global");
@@ -923,6 +933,7 @@ extern "C" int hs_step(hs_sim *sim, void *stream)
                 L.aux[0] = sim->auxStream[b][0]; L.aux[1] = sim->auxStream[b][1];
                 L.auxFork = sim->auxFork[b]; L.auxJoin[0] = sim->auxJoin[b][0]; L.auxJoin[1] = sim->auxJoin[b][1];
             }
+            L.orderedSolve = orderedSolveDefault();
             launchStep(L, sim->cosThreshold, sim->raysNearestFirst);
             launches += L.count;
         }

@@ -1125,12 +1125,13 @@ __device__ __forceinline__ void levelContactList(StagedWorld &sw, int K, int fir
 // by all 32 lanes; a round ends with a warp barrier, which orders the shared-memory body updates
 // of one level before the next.
 template <bool kVelocities>
-__device__ __forceinline__ void sweepList(const DeviceState &S, int w, StagedWorld &sw, int K, int first, int lg,
-                                          const float (*mass)[8])
+__device__ __forceinline__ int sweepList(const DeviceState &S, int w, StagedWorld &sw, int K, int first, int lg,
+                                         const float (*mass)[8])
 {
-    int i = 0;
+    int i = 0, rounds = 0;
     while (__any_sync(kFullMask, i < K)) {
         const bool active = i < K;
+        rounds += active;
         int nd = 0, ns = 0;
         if (active) {
             const int lv = int(sw.list[sw.order[i]].x >> 8) & 0xFF;
@@ -1151,9 +1152,10 @@ __device__ __forceinline__ void sweepList(const DeviceState &S, int w, StagedWor
         i += nd + ns;
         __syncwarp();
     }
+    return rounds;          // rounds this group's world needed (the warp runs the maximum of its four)
 }
 
-__global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceState S, int stageCap, int integrateNext)
+__global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceState S, int stageCap, int integrateNext, int orderIn)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     float (*mass)[8] = reinterpret_cast<float (*)[8]>(smemRaw);
@@ -1163,7 +1165,31 @@ __global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceS
     const int grp = threadIdx.x / kSolveLanes;
     const int wRaw = blockIdx.x * kStagedGroups + grp;
     const bool live = wRaw < S.p.numWorlds;
-    const int w = live ? wRaw : 0;             // idle groups stay in the warp's control flow
+    // ---- which world this group solves ----------------------------------------------------------
+    // A warp runs its four worlds' sweeps in lockstep, i.e. for as many rounds as the slowest of
+    // them needs (3 or 4 for most worlds: 4.25 on average for four neighbours, 3.6 for four alike).
+    // Worlds are independent, so ANY assignment of worlds to groups gives the same results; each
+    // launch therefore files its worlds by the rounds they took (8 buckets, arrival order inside),
+    // and the next substep's launch hands them out bucket by bucket, slowest first.  Four buffers
+    // rotate with the substep index (orderIn): launch i reads buffer i, fills i + 1 and clears the
+    // counters of i + 2.  orderIn < 0 (un-graphed profiling steps, which see the shard as one
+    // slice) or counters that do not add up to this slice's world count: identity order.
+    int w = live ? wRaw : 0;                   // idle groups stay in the warp's control flow
+    const int orderOut = orderIn >= 0 ? (orderIn + 1) % kSolveOrderBufs : -1;
+    if (orderIn >= 0) {
+        const int *cnt = S.solveCnt + orderIn * kSolveOrderBuckets;
+        int total = 0, bucket = -1, base = 0;
+#pragma unroll
+        for (int b = kSolveOrderBuckets - 1; b >= 0; b--) {
+            const int c = cnt[b];
+            if (bucket < 0 && wRaw < total + c) { bucket = b; base = total; }
+            total += c;
+        }
+        if (live && total == S.p.numWorlds && bucket >= 0)
+            w = int(S.solveOrder[size_t(orderIn * kSolveOrderBuckets + bucket) * S.p.stride + (wRaw - base)]);
+        if (blockIdx.x == 0 && threadIdx.x < kSolveOrderBuckets)
+            S.solveCnt[((orderIn + 2) % kSolveOrderBufs) * kSolveOrderBuckets + threadIdx.x] = 0;
+    }
     StagedWorld &sw = *reinterpret_cast<StagedWorld *>(smemRaw + kMassBytes + grp * stagedWorldBytes(stageCap));
 
     int first = 0, count = -1, nc = 0;
@@ -1230,7 +1256,7 @@ __global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceS
     const bool staged = work && !tooMany;
 
     // ---- positions ----------------------------------------------------------------------------
-    sweepList<false>(S, w, sw, K, first, lg, mass);
+    const int rounds = sweepList<false>(S, w, sw, K, first, lg, mass);
     // joints in creation order (at most one Fixed joint per agent), after every contact
     if (staged && lg == 0) {
         const int na = WI(S, WF_NUM_AGENTS, w);
@@ -1304,6 +1330,11 @@ __global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceS
         }
     }
     if (staged && lg == 0) WI(S, WF_NUM_CONTACTS, w) = total;
+    if (orderOut >= 0 && live && lg == 0) {
+        const int b = staged ? min(rounds, kSolveOrderBuckets - 1) : kSolveOrderBuckets - 1;
+        const int pos = atomicAdd(&S.solveCnt[orderOut * kSolveOrderBuckets + b], 1);
+        S.solveOrder[size_t(orderOut * kSolveOrderBuckets + b) * S.p.stride + pos] = uint32_t(w);
+    }
 }
 
 }  // namespace hs

@@ -182,6 +182,8 @@ struct AssetTable {
 //   y: obj a | obj b << 4 | carrying a << 8 | carrying b << 9 | static a << 10 | static b << 11
 struct alignas(8) SchedEntry { uint32_t x, y; };
 
+constexpr int kSolveOrderBufs = 4, kSolveOrderBuckets = 8;     // DeviceState::solveOrder / solveCnt
+
 struct SimParams {
     int numWorlds;           // worlds this launch covers (the whole shard, or one slice of it)
     int stride;              // worlds on the shard = SoA row stride of every per-world array
@@ -206,6 +208,10 @@ struct DeviceState {
     uint8_t *dfsLeaf;        // [N][kDfsStride] leaf ids in BVH visiting order (set by the rebuild)
     uint32_t *resetList;     // [N] worlds to regenerate this step: world | level << 24 (compacted)
     int *resetCount;         // [N] element 0 of a slice's view counts that slice's list
+    // k_solve's world order (a performance hint, any permutation is valid): 4 rotating buffers of
+    // 8 buckets keyed by the rounds a world's contact sweep took in the previous substep
+    uint32_t *solveOrder;    // [4 * 8][N] worlds of a bucket (slice-relative), in arrival order
+    int *solveCnt;           // [N + 64] elements 0..31 of a slice's view: worlds per (buffer, bucket)
     uint16_t *cand;          // [N][kMaxCand]  a | b<<8
     float *contact;          // [N][kMaxCand][kContactWords]
     uint32_t *cmeta;         // [N][kMaxCand]
@@ -250,6 +256,7 @@ inline DeviceState sliceOf(const DeviceState &S, int begin, int count)
     V.bvh += b * kBvhWords;
     V.dfsLeaf += b * kDfsStride;
     V.resetList += b; V.resetCount += b;
+    V.solveOrder += b; V.solveCnt += b;
     V.cand += b * kMaxCand;
     V.contact += b * kMaxCand * kContactWords;
     V.cmeta += b * kMaxCand;

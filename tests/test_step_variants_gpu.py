@@ -16,7 +16,7 @@ from compact import hs_dump_compact, hs_set_debug
 pytestmark = pytest.mark.gpu
 
 
-KNOBS = ("HIDESEEK_HEAD_REFIT", "HIDESEEK_FUSED_SUBSTEP")
+KNOBS = ("HIDESEEK_HEAD_REFIT", "HIDESEEK_FUSED_SUBSTEP", "HIDESEEK_SOLVE_ORDER")
 
 
 def _run(env, N=384, steps=250):
@@ -86,3 +86,13 @@ def test_substep_at_the_tail_of_the_solver_is_the_substep_kernel():
     l0, fused = _run({})
     assert l1 > l0 and (l1 - l0) % 3 == 0, (l1, l0)          # three launches per world slice
     _same(launched, fused)
+
+
+def test_solver_world_order_is_only_a_schedule():
+    """k_solve hands its worlds out grouped by the rounds their contact sweeps took in the previous
+    substep (HIDESEEK_SOLVE_ORDER=0: index order).  Worlds are independent, so which warp solves a
+    world must not show in any bit of the result."""
+    l1, plain = _run({"HIDESEEK_SOLVE_ORDER": "0"})
+    l0, ordered = _run({})
+    assert l1 == l0
+    _same(plain, ordered)
