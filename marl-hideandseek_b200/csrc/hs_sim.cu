@@ -47,6 +47,9 @@ struct hs_sim {
     std::vector<void *> allocs;
     hs_world_dump *dumpDev = nullptr;
     int lastLaunches = 0;
+    // who filled the k_solve world-order buffers last: 0 nobody, 1 the step graph (per-slice views),
+    // 2 hs_step_profiled (one whole-shard view); a change of view clears the counters (= identity order)
+    int orderView = 0;
     cudaGraphExec_t stepGraph = nullptr;
     cudaStream_t graphStream = nullptr;
     // The step graph runs the shard as `slices` independent world ranges on parallel branches:
@@ -593,7 +596,7 @@ struct Launcher {
     bool stagedSolve = stagedSolveDefault();
     bool headRefit = headRefitDefault();
     bool fusedSubstep = fusedSubstepDefault();
-    bool orderedSolve = false;          // set by the step-graph capture only (fixed slices): see k_solve
+    bool orderedSolve = false;          // set by hs_step (graph capture) and hs_step_profiled, which own the order buffers
     // graph capture only: side streams + events for the independent observation-stage kernels
     cudaStream_t aux[2] = {nullptr, nullptr};
     cudaEvent_t auxFork = nullptr, auxJoin[2] = {nullptr, nullptr};
@@ -948,6 +951,10 @@ extern "C" int hs_step(hs_sim *sim, void *stream)
         HS_CUDA(cudaGraphDestroy(graph));
         sim->lastLaunches = L.count;
     }
+    if (sim->orderView != 1) {
+        HS_CUDA(cudaMemsetAsync(sim->S.solveCnt, 0, sizeof(int) * (size_t(sim->cfg.num_worlds) + 64), st));
+        sim->orderView = 1;
+    }
     HS_CUDA(cudaGraphLaunch(sim->stepGraph, st));
     return 0;
 }
@@ -1144,9 +1151,14 @@ extern "C" int hs_step_profiled(hs_sim *sim, void *stream, float *ms_out, int ca
     cudaEvent_t start;
     HS_CUDA(cudaEventCreate(&start));
     HS_CUDA(cudaEventRecord(start, st));
+    if (sim->orderView != 2) {
+        HS_CUDA(cudaMemsetAsync(sim->S.solveCnt, 0, sizeof(int) * (size_t(sim->cfg.num_worlds) + 64), st));
+        sim->orderView = 2;
+    }
     Launcher L{sim->S, st};
     L.events = &ev;
     L.names = &g_profNames;
+    L.orderedSolve = orderedSolveDefault();
     launchStep(L, sim->cosThreshold, sim->raysNearestFirst);
     HS_CUDA(cudaStreamSynchronize(st));
     cudaEvent_t prev = start;

@@ -1172,8 +1172,9 @@ __global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceS
     // launch therefore files its worlds by the rounds they took (8 buckets, arrival order inside),
     // and the next substep's launch hands them out bucket by bucket, slowest first.  Four buffers
     // rotate with the substep index (orderIn): launch i reads buffer i, fills i + 1 and clears the
-    // counters of i + 2.  orderIn < 0 (un-graphed profiling steps, which see the shard as one
-    // slice) or counters that do not add up to this slice's world count: identity order.
+    // counters of i + 2.  Counters that do not add up to this view's world count (first launch, or
+    // hs_sim.cu cleared them because the caller's view of the shard changed — step graph: world
+    // slices, hs_step_profiled: one range) or orderIn < 0: identity order.
     int w = live ? wRaw : 0;                   // idle groups stay in the warp's control flow
     const int orderOut = orderIn >= 0 ? (orderIn + 1) % kSolveOrderBufs : -1;
     if (orderIn >= 0) {
