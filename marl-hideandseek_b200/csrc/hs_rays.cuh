@@ -31,6 +31,9 @@ namespace hs {
 #define HS_RAY_THREADS 160
 #endif
 constexpr int kRayThreads = HS_RAY_THREADS;
+#ifndef HS_RAY_MINB
+#define HS_RAY_MINB 8
+#endif
 constexpr int kMaxVisRays = kMaxAgents * (kMaxBoxes + kMaxRamps + kMaxAgents - 1);   // 96
 constexpr int kMaxRays = kMaxAgents * 30 + kMaxVisRays;                               // 276 per world
 constexpr int kRayQueueA = 1024, kRayQueueB = 384;
@@ -38,8 +41,13 @@ static_assert(kMaxRays <= 512 && kMaxBodies <= 64, "queue entries pack a ray in 
 
 __constant__ float c_lidarDir[30][2];     // (cos, sin) of theta_i, hs_det_sincosf on the host
 
-struct RaySmem {
-    uint32_t bvh[kBvhWords];
+// kFullBvh = false (the flat nearest-first query, which never touches the inner nodes) keeps only
+// the leaf records: 4.2 KB instead of the 13 KB blob, which is what lets an SM hold 8 CTAs.
+// blob() is the address the blob WOULD start at, so kBvhLeafOff-based accessors work unchanged.
+template <bool kFullBvh>
+struct RaySmemT {
+    uint32_t bvh[kFullBvh ? kBvhWords : kMaxBodies * kLeafWords];
+    __device__ __forceinline__ uint32_t *blob() { return bvh - (kFullBvh ? 0 : kBvhLeafOff); }
     AssetTable assets;
     float agentPos[kMaxAgents][3];
     float agentRot[kMaxAgents][4];
@@ -324,21 +332,23 @@ __device__ __forceinline__ bool leafSlab(const float *L, Vec3 o, Vec3 inv, float
 }
 
 // hull test of (ray r, leaf) merged into the ray's key; `o` = the ray's origin
-__device__ __forceinline__ void rayTestLeaf(RaySmem &sm, int r, int leaf, Vec3 o)
+template <class SM>
+__device__ __forceinline__ void rayTestLeaf(SM &sm, int r, int leaf, Vec3 o)
 {
     const Vec3 d = {sm.rayD[r][0], sm.rayD[r][1], sm.rayD[r][2]};
     const float best = rayKeyT(*(volatile unsigned long long *)&sm.rayKey[r]);
     float t;
-    if (traceLeafS(sm.bvh, sm.assets, leaf, o, d, best, &t)) atomicMin(&sm.rayKey[r], rayKeyPack(t, leaf));
+    if (traceLeafS(sm.blob(), sm.assets, leaf, o, d, best, &t)) atomicMin(&sm.rayKey[r], rayKeyPack(t, leaf));
 }
 
 // slab re-check of (ray r, leaf) against the ray's best hit so far; survivors go to list B
-__device__ __forceinline__ void rayRecheckLeaf(RaySmem &sm, int r, int leaf, Vec3 o)
+template <class SM>
+__device__ __forceinline__ void rayRecheckLeaf(SM &sm, int r, int leaf, Vec3 o)
 {
     const Vec3 inv = {sm.rayInv[r][0], sm.rayInv[r][1], sm.rayInv[r][2]};
     const float best = rayKeyT(*(volatile unsigned long long *)&sm.rayKey[r]);
     float a;
-    if (!leafSlab(leafF(sm.bvh, leaf), o, inv, best, &a)) return;
+    if (!leafSlab(leafF(sm.blob(), leaf), o, inv, best, &a)) return;
     const int i = atomicAdd(&sm.qbCount, 1);
     if (i < kRayQueueB) sm.qb[i] = uint16_t(r | (leaf << 9));
     else rayTestLeaf(sm, r, leaf, o);
@@ -355,9 +365,10 @@ __device__ __forceinline__ int traceRaySel(const uint32_t *blob, const AssetTabl
 }
 
 template <bool kNearestFirst>
-__global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosThreshold)
+__global__ void __launch_bounds__(kRayThreads, HS_RAY_MINB) k_rays(DeviceState S, float cosThreshold)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
+    using RaySmem = RaySmemT<!kNearestFirst>;
     RaySmem &sm = *reinterpret_cast<RaySmem *>(smemRaw);
     const int w = blockIdx.x;
     const int tid = threadIdx.x;
@@ -368,9 +379,9 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
     const int numNodes = min((int)g[0], kMaxNodes), numLeaves = min((int)g[1], kMaxBodies);
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(g);
-        uint4 *dst = reinterpret_cast<uint4 *>(sm.bvh);
-        // the flat query never touches the inner nodes: header only
-        const int nodeVec = kNearestFirst ? kBvhNodeOff / 4 : (kBvhNodeOff + numNodes * kNodeWords) / 4;
+        uint4 *dst = reinterpret_cast<uint4 *>(sm.blob());
+        // the flat query never touches the header or the inner nodes (and has no room for them)
+        const int nodeVec = kNearestFirst ? 0 : (kBvhNodeOff + numNodes * kNodeWords) / 4;
         for (int i = tid; i < nodeVec; i += kRayThreads) dst[i] = src[i];
         // the world's leaf records are one contiguous, 16-byte aligned run of numLeaves * 80 bytes:
         // ONE bulk-async copy (TMA engine), completion counted on an mbarrier; it overlaps the
@@ -384,7 +395,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
                 const uint32_t bytes = uint32_t(numLeaves) * kLeafWords * 4u;
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                             ::"r"((uint32_t)__cvta_generic_to_shared(sm.bvh + kBvhLeafOff)), "l"(g + kBvhLeafOff), "r"(bytes), "r"(bar)
+                             ::"r"((uint32_t)__cvta_generic_to_shared(sm.blob() + kBvhLeafOff)), "l"(g + kBvhLeafOff), "r"(bytes), "r"(bar)
                              : "memory");
             }
         }
@@ -417,7 +428,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
         if (sm.agentSlot[tid] >= 0) {
             const int leaf = metaLeaf(META(S, sm.agentSlot[tid], w));
             Vec3 p = {sm.agentPos[tid][0], sm.agentPos[tid][1], sm.agentPos[tid][2]};
-            if (leaf < numLeaves && originInsideLeaf(sm.bvh, sm.assets, leaf, p)) skip = leaf;
+            if (leaf < numLeaves && originInsideLeaf(sm.blob(), sm.assets, leaf, p)) skip = leaf;
         }
         sm.agentSkipLeaf[tid] = skip;
     }
@@ -507,7 +518,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
                 int bestL = -1;
                 for (int l = 0; l < numLeaves; l++) {
                     float a;
-                    const bool ok = leafSlab(leafF(sm.bvh, l), o, inv, tmax, &a);
+                    const bool ok = leafSlab(leafF(sm.blob(), l), o, inv, tmax, &a);
                     if (ok && l != skipLeaf) {
                         mask |= 1ull << l;
                         if (a < bestA) { bestA = a; bestL = l; }
@@ -515,7 +526,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
                 }
                 if (bestL >= 0) {
                     float t;
-                    if (traceLeafS(sm.bvh, sm.assets, bestL, o, d, tmax, &t)) key = rayKeyPack(t, bestL);
+                    if (traceLeafS(sm.blob(), sm.assets, bestL, o, d, tmax, &t)) key = rayKeyPack(t, bestL);
                     mask &= ~(1ull << bestL);
                 }
                 sm.rayD[r][0] = d.x; sm.rayD[r][1] = d.y; sm.rayD[r][2] = d.z;
@@ -555,7 +566,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
             const unsigned long long key = sm.rayKey[r];
             const unsigned low = (unsigned)key;
             const int hit = low == 0xFFFFFFFFu ? -1
-                          : int(sm.bvh[kBvhLeafOff + int(0x7FFFFFFFu - low) * kLeafWords + kLeafInfo] & 0xFF);
+                          : int(sm.blob()[kBvhLeafOff + int(0x7FFFFFFFu - low) * kLeafWords + kLeafInfo] & 0xFF);
             const float t = rayKeyT(key);
             if (r < numLidar) {
                 const int k = r / 30;
@@ -602,7 +613,7 @@ __global__ void __launch_bounds__(kRayThreads) k_rays(DeviceState S, float cosTh
             o = {sm.agentPos[k][0], sm.agentPos[k][1], sm.agentPos[k][2]};
         }
         float t = 0.f;
-        int hit = traceRaySel<kNearestFirst>(sm.bvh, sm.assets, active, o, d, tmax, &t, active ? sm.agentSkipLeaf[k] : -1);
+        int hit = traceRaySel<kNearestFirst>(sm.blob(), sm.assets, active, o, d, tmax, &t, active ? sm.agentSkipLeaf[k] : -1);
         if (!active) continue;
         if (isLidar) {
             S.exLidar[(size_t(w) * A + k) * 30 + (r - k * 30)] = hit < 0 ? 0.f : t;

@@ -189,8 +189,8 @@ static int createBody(hs_sim *sim, const hs_config *cfg, int A)
             dirs[i][0] = cs; dirs[i][1] = sn;
         }
         HS_CUDA(cudaMemcpyToSymbol(c_lidarDir, dirs, sizeof(dirs)));
-        HS_CUDA(cudaFuncSetAttribute(k_rays<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
-        HS_CUDA(cudaFuncSetAttribute(k_rays<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmem)));
+        HS_CUDA(cudaFuncSetAttribute(k_rays<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmemT<false>)));
+        HS_CUDA(cudaFuncSetAttribute(k_rays<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RaySmemT<true>)));
         HS_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, solveSmemBytes(kStageMax)));
         HS_CUDA(cudaFuncSetAttribute(k_narrowphase, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NpSmem)));
         if (const char *e = getenv("HIDESEEK_RAY_ORDER")) sim->raysNearestFirst = strcmp(e, "reference") != 0;
@@ -651,8 +651,8 @@ void launchObservations(Launcher &L, float cosThr, bool nearestFirst)
         const long long nb = obsBlocks(R) + obsBlocks(R * kMaxBoxes) + obsBlocks(R * kMaxRamps) + obsBlocks(R * kMaxAgents);
         k_observations<<<unsigned(nb), kObsThreads, 0, so>>>(L.S);
     } L.mark("k_observations");
-    if (nearestFirst) k_rays<true><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
-    else k_rays<false><<<L.N(), kRayThreads, sizeof(RaySmem), L.st>>>(L.S, cosThr);
+    if (nearestFirst) k_rays<true><<<L.N(), kRayThreads, sizeof(RaySmemT<false>), L.st>>>(L.S, cosThr);
+    else k_rays<false><<<L.N(), kRayThreads, sizeof(RaySmemT<true>), L.st>>>(L.S, cosThr);
     L.mark("k_rays");
     k_debug_positions<<<L.gWorld(), 128, 0, sd>>>(L.S); L.mark("k_debug_positions");
     if (fork) {
