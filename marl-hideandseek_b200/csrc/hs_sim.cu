@@ -689,7 +689,10 @@ void launchStep(Launcher &L, float cosThr, bool nearestFirst)
         k_narrowphase<<<(L.N() + kNpWorlds - 1) / kNpWorlds, kNpThreads, sizeof(NpSmem), L.st>>>(L.S); L.mark("k_narrowphase");
         if (L.fusedSolve && L.stagedSolve) {
             // body area of the staged solver: 9 boxes + 2 ramps + ground plane + this Manager's agent slots
-            const int stageCap = kMaxBoxes + kMaxRamps + 1 + L.S.p.agentsPerWorld;
+            int stageCap = kMaxBoxes + kMaxRamps + 1 + L.S.p.agentsPerWorld;
+            // test knob: a smaller body area sends the worlds that do not fit down the kernel's
+            // global-memory path (tests/test_step_variants_gpu.py), which generated levels never take
+            if (const char *e = getenv("HIDESEEK_STAGE_CAP")) stageCap = std::max(1, std::min(stageCap, atoi(e)));
             k_solve<<<(L.N() + kStagedGroups - 1) / kStagedGroups, kStagedThreads, solveSmemBytes(stageCap), L.st>>>(
                 L.S, stageCap, tailSubstep && i + 1 < kSubsteps ? 1 : 0, L.orderedSolve ? i % kSolveOrderBufs : -1);
             L.mark("k_solve");

@@ -16,7 +16,7 @@ from compact import hs_dump_compact, hs_set_debug
 pytestmark = pytest.mark.gpu
 
 
-KNOBS = ("HIDESEEK_HEAD_REFIT", "HIDESEEK_FUSED_SUBSTEP", "HIDESEEK_SOLVE_ORDER")
+KNOBS = ("HIDESEEK_HEAD_REFIT", "HIDESEEK_FUSED_SUBSTEP", "HIDESEEK_SOLVE_ORDER", "HIDESEEK_STAGE_CAP")
 
 
 def _run(env, N=384, steps=250):
@@ -96,3 +96,14 @@ def test_solver_world_order_is_only_a_schedule():
     l0, ordered = _run({})
     assert l1 == l0
     _same(plain, ordered)
+
+
+def test_global_memory_fallback_of_the_staged_solver():
+    """A world whose movable bodies do not fit the solver's shared-memory body area is solved (and,
+    for substeps 2-4, integrated) out of global memory inside the same kernel.  Generated levels
+    always fit, so the path is forced here: with room for 10 bodies most worlds fall back, a few
+    stay staged, and every world record must still match the default build's bit for bit."""
+    l1, forced = _run({"HIDESEEK_STAGE_CAP": "10"})
+    l0, default = _run({})
+    assert l1 == l0
+    _same(forced, default)
