@@ -23,7 +23,7 @@ def _run(env, N=384, steps=250):
     import gpu_hideseek as gh
     for k in KNOBS:
         os.environ.pop(k, None)
-    os.environ.update(env)
+    os.environ.update({k: v for k, v in env.items() if not k.startswith("_")})
     try:
         sim = gh.HideAndSeekSimulator(num_worlds=N, rand_seed=11, min_hiders=1, max_hiders=3,
                                       min_seekers=1, max_seekers=3)
@@ -48,7 +48,10 @@ def _run(env, N=384, steps=250):
             if step == 130:
                 for w in (3, 200):
                     sim.load_checkpoint(w)
-            sim.step()
+            if env.get("_PROFILED_EVERY") and step % int(env["_PROFILED_EVERY"]) == 2:
+                sim.step_profiled()              # un-graphed launches of the same step, whole shard as one range
+            else:
+                sim.step()
             if launches is None:
                 launches = sim.last_step_launches()
             if step % 20 == 0 or step in (61, 131, 239, 240, 241):
@@ -107,3 +110,12 @@ def test_global_memory_fallback_of_the_staged_solver():
     l0, default = _run({})
     assert l1 == l0
     _same(forced, default)
+
+
+def test_profiled_steps_interleave_with_graph_steps():
+    """hs_step_profiled (what bench.py times kernels with) runs the step as plain launches over the
+    whole shard, the step graph as world slices; both use the solver's world-order buffers, which are
+    cleared whenever the view changes.  Mixing the two must not change a bit."""
+    _, mixed = _run({"_PROFILED_EVERY": "5"})
+    _, graph = _run({})
+    _same(mixed, graph)
