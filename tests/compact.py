@@ -127,7 +127,8 @@ def compare_compact(r, h, tol=1e-4, exact=False, check_scores=True, probes=True,
     bad("node_children", (r["node_children"] != h["node_children"]) & nodelive[:, :, None])
     bad("node_parent", (r["node_parent"] != h["node_parent"]) & nodelive)
     child_live = (r["node_children"] != -1) & nodelive[:, :, None]          # [n, NODES, 4]
-    db = np.where(child_live[:, :, None, :], np.abs(r["node_bounds"].astype(np.float64) - h["node_bounds"]), 0.0)
+    with np.errstate(invalid="ignore"):                # inf - inf of equal infinite bounds (the ground plane)
+        db = np.where(child_live[:, :, None, :], np.abs(r["node_bounds"].astype(np.float64) - h["node_bounds"]), 0.0)
     db = np.nan_to_num(db, nan=0.0, posinf=np.inf)       # inf - inf of equal infinite bounds
     eqb = (_bits(r["node_bounds"]) == _bits(h["node_bounds"])) | ~child_live[:, :, None, :]
     stats["max_node_bounds"] = float(np.where(eqb, 0.0, db).max()) if n else 0.0
