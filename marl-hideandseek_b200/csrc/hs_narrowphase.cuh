@@ -136,9 +136,12 @@ __device__ inline EdgeQuery queryEdgeRange(const WorldHull &a, const WorldHull &
             }
             if (sep > q.sep) {
                 q.sep = sep; q.normal = normal; q.edgeA = ha; q.edgeB = hb;
-                if (q.sep > 0.f) return q;
             }
         }
+        // the reference leaves at the first positive separation; only its sign is used then, and the
+        // running maximum stays positive, so the exit can wait for the end of the row (the inner
+        // loop is branch-free apart from the rare Minkowski-face hit and can be pipelined)
+        if (q.sep > 0.f) return q;
     }
     return q;
 }
