@@ -497,7 +497,10 @@ __global__ void __launch_bounds__(kNpThreads, HS_NP_MINB) k_narrowphase(DeviceSt
         __syncwarp();
         const WorldHull ha = viewHull(sm.hull[tid & ~1], HA), hb = viewHull(sm.hull[tid | 1], HB);
 
-        FaceQuery mine = half ? queryFaces(hb, ha) : queryFaces(ha, hb);
+        // one call site: `half ? queryFaces(hb, ha) : queryFaces(ha, hb)` would be two inlined copies that
+        // the two lanes of every pair run one after the other
+        const WorldHull fx = half ? hb : ha, fy = half ? ha : hb;
+        FaceQuery mine = queryFaces(fx, fy);
         __syncwarp();
         FaceQuery other;
         other.sep = __shfl_xor_sync(0xFFFFFFFFu, mine.sep, 1);
