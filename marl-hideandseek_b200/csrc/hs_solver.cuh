@@ -160,14 +160,21 @@ __device__ __forceinline__ ContactView loadContact(const float *c, uint32_t meta
 // getAvgContact: returns true when the contact has zero total penetration
 __device__ __forceinline__ bool avgContact(const ContactView &c, Vec3 *avg, float *pen)
 {
+    // fixed trip counts with a predicate (same operations in the same order): static indices keep the
+    // contact in registers
     float maxPen = -FLT_MAX, sum = 0.f;
-    for (int i = 0; i < c.n; i++) {
-        if (c.depth[i] > maxPen) maxPen = c.depth[i];
-        sum += c.depth[i];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if (i < c.n) {
+            if (c.depth[i] > maxPen) maxPen = c.depth[i];
+            sum += c.depth[i];
+        }
     }
     if (sum == 0.f) return true;
     Vec3 a = {0.f, 0.f, 0.f};
-    for (int i = 0; i < c.n; i++) a += (c.depth[i] / sum) * c.pts[i];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (i < c.n) a += (c.depth[i] / sum) * c.pts[i];
     *avg = a;
     *pen = maxPen;
     return false;
@@ -510,7 +517,9 @@ __device__ inline void solveContactVelocity(const DeviceState &S, int w, uint32_
     }
 
     float penSum = 0.f;
-    for (int i = 0; i < c.n; i++) penSum += c.depth[i];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (i < c.n) penSum += c.depth[i];
 
     for (int i = 0; i < c.n; i++) {
         Vec3 r1, r2;
@@ -950,7 +959,9 @@ __device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int 
     }
 
     float penSum = 0.f;
-    for (int i = 0; i < c.n; i++) penSum += c.depth[i];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (i < c.n) penSum += c.depth[i];
 
     // not unrolled: four copies of the friction update are 1100 more instructions in the solver's
     // hottest loop, and the instruction cache notices (1.457 -> 1.411 ms per step)
@@ -958,8 +969,14 @@ __device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int 
     for (int i = 0; i < 4; i++) {
         const bool pt = act && i < c.n;
         Vec3 r = zero, ai = zero;
+        // point i comes from the contact row again (a 16-byte load that hits L1): indexing the register
+        // copy with the loop counter would push the whole contact into local memory
+        float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pt) p4 = reinterpret_cast<const float4 *>(row)[i];
+        const Vec3 cpt = {p4.x, p4.y, p4.z};
+        const float cdepth = p4.w;
         if (pt) {
-            const Vec3 contact = side ? c.pts[i] - n * c.depth[i] : c.pts[i];
+            const Vec3 contact = side ? cpt - n * cdepth : cpt;
             r = rotate(qinv(pre.q), contact - pre.x);
             const Vec3 rw = rotate(q, r);
             ai = v + cross(o, rw);
@@ -987,7 +1004,7 @@ __device__ __forceinline__ void pairContactVelocities(const DeviceState &S, int 
         float wio = __shfl_xor_sync(kFullMask, wi, 1);
         if (solo) wio = 0.f;
         if (go) {
-            const float lambda = lambdaN * (c.depth[i] / penSum);
+            const float lambda = lambdaN * (cdepth / penSum);
             const float invScale = 1.f / ((side ? wio : wi) + (side ? wi : wio));
             const float fmag = P.muD * fabsf(lambda) * invScale / h;
             const float corrected = -fminf(fmag, vtLen);
