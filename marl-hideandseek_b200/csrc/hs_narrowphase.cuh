@@ -307,7 +307,8 @@ __device__ inline Manifold faceContact(Plane ref, int refFace, int incFace,
     return buildManifold(ref.n, in, depth, below);
 }
 
-__device__ inline Manifold facePlaneContact(Plane pl, int incFace, const WorldHull &Hh)
+// createFacePlaneContact for a face of any size (the reference's form: arrays indexed as they fill)
+__device__ __noinline__ Manifold facePlaneContactGeneric(Plane pl, int incFace, const WorldHull &Hh)
 {
     Vec3 pts[kClipCap];
     float depth[kClipCap];
@@ -325,6 +326,54 @@ __device__ inline Manifold facePlaneContact(Plane pl, int incFace, const WorldHu
         }
     } while (he != start);
     return buildManifold(pl.n, pts, depth, n);
+}
+
+// The same for faces of at most four vertices — every face of this environment's hulls — without
+// arrays that fill at a running index: those live in local memory, and with 2 x 97 KB of shared
+// memory per SM there is little L1 left to keep them in.  Candidates stay in registers and are
+// packed into the manifold's slots by selects, in the same order, through the same operations.
+__device__ inline Manifold facePlaneContact(Plane pl, int incFace, const WorldHull &Hh)
+{
+    const HullData &H = *Hh.h;
+    const int start = H.faceBase[incFace];
+    int he = start;
+    bool more = true;
+    Vec3 pv[4];
+    float pd[4];
+    bool ok[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        ok[k] = false;
+        pv[k] = {0.f, 0.f, 0.f};
+        pd[k] = 0.f;
+        if (more) {
+            const Vec3 v = Hh.v[H.hedgeRoot[he]];
+            he = H.hedgeNext[he];
+            const float d = distFromPlane(pl, v);
+            if (d <= 0.0f) {
+                pv[k] = v - d * pl.n;
+                pd[k] = -d;
+                ok[k] = true;
+            }
+            more = he != start;
+        }
+    }
+    if (more) return facePlaneContactGeneric(pl, incFace, Hh);       // a face with more than four vertices
+    const int c1 = ok[0], c2 = c1 + ok[1], c3 = c2 + ok[2];
+    Manifold m;
+    m.n = c3 + ok[3];
+    const Quat id = {1.f, 0.f, 0.f, 0.f};
+    const Vec3 zero = {0.f, 0.f, 0.f};
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const bool s0 = ok[0] && j == 0, s1 = ok[1] && c1 == j, s2 = ok[2] && c2 == j, s3 = ok[3] && c3 == j;
+        const Vec3 p = s0 ? pv[0] : s1 ? pv[1] : s2 ? pv[2] : pv[3];
+        m.depth[j] = s0 ? pd[0] : s1 ? pd[1] : s2 ? pd[2] : pd[3];
+        m.pts[j] = j < m.n ? rotate(id, p) + zero : p;          // buildManifold's tail, see there
+        (void)s3;
+    }
+    m.normal = rotate(id, pl.n);
+    return m;
 }
 
 __device__ inline Manifold edgeContact(const EdgeQuery &q, const WorldHull &a, const WorldHull &b)
