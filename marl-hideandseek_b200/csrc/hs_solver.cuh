@@ -1175,7 +1175,7 @@ __device__ __forceinline__ int sweepList(const DeviceState &S, int w, StagedWorl
     return rounds;          // rounds this group's world needed (the warp runs the maximum of its four)
 }
 
-__global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(DeviceState S, int stageCap, int integrateNext, int orderIn)
+__global__ void __launch_bounds__(kStagedThreads, HS_SOLVE_MINB) k_solve(const __grid_constant__ DeviceState S, int stageCap, int integrateNext, int orderIn)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     float (*mass)[8] = reinterpret_cast<float (*)[8]>(smemRaw);
